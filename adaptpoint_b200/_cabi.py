@@ -1,0 +1,90 @@
+"""ctypes binding of libapb200.so (include/apb200.h).
+
+The product path has NO fallback: if the CUDA library is missing or a call returns a non-zero
+status this module raises.  Tensors are passed as raw device pointers plus the current torch CUDA
+stream, mirroring how the reference's pybind wrappers receive pre-allocated tensors
+(openpoints/cpp/pointnet2_batch/src/pointnet2_api.cpp:10-24).
+"""
+import ctypes
+import os
+
+import torch
+
+_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libapb200.so")
+_lib = None
+
+_i, _f, _p = ctypes.c_int, ctypes.c_float, ctypes.c_void_p
+
+# name -> argtypes (all return int status unless noted)
+_SIGNATURES = {
+    "apb_fps_f32": [_p, _p, _p, _i, _i, _i, _p],
+    "apb_gather_f32": [_p, _p, _p, _i, _i, _i, _i, _p],
+    "apb_gather_grad_f32": [_p, _p, _p, _i, _i, _i, _i, _p],
+    "apb_ball_query_f32": [_p, _p, _p, _i, _i, _i, _f, _i, _p],
+    "apb_knn_f32": [_p, _p, _p, _p, _i, _i, _i, _i, _p],
+    "apb_group_f32": [_p, _p, _p, _i, _i, _i, _i, _i, _p],
+    "apb_group_grad_f32": [_p, _p, _p, _i, _i, _i, _i, _i, _p],
+    "apb_three_nn_f32": [_p, _p, _p, _p, _i, _i, _i, _p],
+    "apb_three_interp_f32": [_p, _p, _p, _p, _i, _i, _i, _i, _p],
+    "apb_three_interp_grad_f32": [_p, _p, _p, _p, _i, _i, _i, _i, _p],
+}
+EXPORTED_SYMBOLS = sorted(list(_SIGNATURES) + ["apb_version", "apb_error_string", "apb_fps_block_size"])
+
+
+class ApbError(RuntimeError):
+    pass
+
+
+def lib_path():
+    return _LIB_PATH
+
+
+def load():
+    """Load libapb200.so once; raise loudly if it has not been built (no CPU fallback exists)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(_LIB_PATH):
+        raise ApbError(
+            f"{_LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(adaptpoint_b200 has no CPU or PyTorch fallback path)")
+    lib = ctypes.CDLL(_LIB_PATH)
+    for name, argtypes in _SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.argtypes = argtypes
+        fn.restype = _i
+    lib.apb_version.restype = ctypes.c_char_p
+    lib.apb_version.argtypes = []
+    lib.apb_error_string.restype = ctypes.c_char_p
+    lib.apb_error_string.argtypes = [_i]
+    lib.apb_fps_block_size.restype = _i
+    lib.apb_fps_block_size.argtypes = [_i]
+    _lib = lib
+    return lib
+
+
+def version():
+    return load().apb_version().decode()
+
+
+def fps_block_size(n):
+    return load().apb_fps_block_size(int(n))
+
+
+def _ptr(t):
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise ApbError("adaptpoint_b200 ops need CUDA tensors (there is no CPU path)")
+    return ctypes.c_void_p(t.data_ptr())
+
+
+def call(name, tensors_and_scalars, device):
+    """Invoke one C-ABI entry point on `device`'s current stream and raise on a non-zero status."""
+    lib = load()
+    with torch.cuda.device(device):
+        stream = ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+        args = [(_ptr(a) if (a is None or isinstance(a, torch.Tensor)) else a) for a in tensors_and_scalars]
+        status = getattr(lib, name)(*args, stream)
+    if status != 0:
+        raise ApbError(f"{name} failed: {lib.apb_error_string(status).decode()} (status {status})")

@@ -1,0 +1,214 @@
+"""The reference's pointnet2_batch operator API over libapb200.so.
+
+Same names, argument order, dtypes and layouts as
+  openpoints/models/layers/subsample.py:76-156   (FurthestPointSampling, GatherOperation, fps)
+  openpoints/models/layers/group.py:76-203       (GroupingOperation, GatherOperation, BallQuery)
+  openpoints/models/layers/upsampling.py:11-102  (ThreeNN, ThreeInterpolate, three_interpolation)
+Differences: outputs are allocated on the INPUT's device (the reference's legacy
+`torch.cuda.FloatTensor(...)` ctors use the current device and ignore `device=`), kernels run on
+torch's current stream, and errors raise instead of exit(-1).  There is no CPU path: CPU tensors
+raise `ApbError`.
+"""
+from typing import Tuple
+
+import torch
+from torch.autograd import Function
+
+from . import _cabi
+
+
+def _check(t, name, dtype=None):
+    if not t.is_cuda:
+        raise _cabi.ApbError(f"{name}: CUDA tensor required (adaptpoint_b200 has no CPU path)")
+    assert t.is_contiguous(), f"{name} must be contiguous"
+    if dtype is not None and t.dtype != dtype:
+        raise TypeError(f"{name}: expected {dtype}, got {t.dtype}")
+
+
+class FurthestPointSampling(Function):
+    @staticmethod
+    def forward(ctx, xyz: torch.Tensor, npoint: int) -> torch.Tensor:
+        """xyz (B,N,3) f32 -> idx (B,npoint) int32; reference subsample.py:77-100."""
+        _check(xyz, "xyz", torch.float32)
+        B, N, _ = xyz.size()
+        output = torch.empty((B, npoint), dtype=torch.int32, device=xyz.device)
+        # temp=None: the kernel keeps the running min-distance (the reference's 1e10-filled scratch,
+        # subsample.py:94) in registers and never spills it to HBM.
+        _cabi.call("apb_fps_f32", [xyz, None, output, B, N, int(npoint)], xyz.device)
+        ctx.mark_non_differentiable(output)
+        return output
+
+    @staticmethod
+    def backward(ctx, a=None):
+        return None, None
+
+
+furthest_point_sample = FurthestPointSampling.apply
+
+
+class GatherOperation(Function):
+    @staticmethod
+    def forward(ctx, features: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+        """features (B,C,N), idx (B,npoint) int32 -> (B,C,npoint); reference subsample.py:108-129."""
+        _check(features, "features", torch.float32)
+        _check(idx, "idx", torch.int32)
+        B, npoint = idx.size()
+        _, C, N = features.size()
+        output = torch.empty((B, C, npoint), dtype=torch.float32, device=features.device)
+        _cabi.call("apb_gather_f32", [features, idx, output, B, C, N, npoint], features.device)
+        ctx.for_backwards = (idx, C, N)
+        return output
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        idx, C, N = ctx.for_backwards
+        B, npoint = idx.size()
+        grad_features = torch.zeros((B, C, N), dtype=torch.float32, device=grad_out.device)
+        grad_out_data = grad_out.detach().contiguous().float()
+        _cabi.call("apb_gather_grad_f32", [grad_out_data, idx, grad_features, B, C, N, npoint], grad_out.device)
+        return grad_features, None
+
+
+gather_operation = GatherOperation.apply
+
+
+class BallQuery(Function):
+    @staticmethod
+    def forward(ctx, radius: float, nsample: int, xyz: torch.Tensor, new_xyz: torch.Tensor) -> torch.Tensor:
+        """xyz (B,N,3) support, new_xyz (B,npoint,3) centres -> idx (B,npoint,nsample) int32;
+        reference group.py:177-196 (note its wrapper takes new_xyz before xyz)."""
+        _check(new_xyz, "new_xyz", torch.float32)
+        _check(xyz, "xyz", torch.float32)
+        B, N, _ = xyz.size()
+        npoint = new_xyz.size(1)
+        idx = torch.empty((B, npoint, nsample), dtype=torch.int32, device=xyz.device)
+        _cabi.call("apb_ball_query_f32", [new_xyz, xyz, idx, B, N, npoint, float(radius), int(nsample)], xyz.device)
+        ctx.mark_non_differentiable(idx)
+        return idx
+
+    @staticmethod
+    def backward(ctx, a=None):
+        return None, None, None, None
+
+
+ball_query = BallQuery.apply
+
+
+class GroupingOperation(Function):
+    @staticmethod
+    @torch.amp.custom_fwd(device_type="cuda", cast_inputs=torch.float32)
+    def forward(ctx, features: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+        """features (B,C,N), idx (B,npoint,nsample) int32 -> (B,C,npoint,nsample); group.py:76-98."""
+        _check(features, "features", torch.float32)
+        _check(idx, "idx", torch.int32)
+        B, nfeatures, nsample = idx.size()
+        _, C, N = features.size()
+        output = torch.empty((B, C, nfeatures, nsample), dtype=torch.float32, device=features.device)
+        _cabi.call("apb_group_f32", [features, idx, output, B, C, N, nfeatures, nsample], features.device)
+        ctx.for_backwards = (idx, N)
+        return output
+
+    @staticmethod
+    @torch.amp.custom_bwd(device_type="cuda")
+    def backward(ctx, grad_out: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+        idx, N = ctx.for_backwards
+        B, C, npoint, nsample = grad_out.size()
+        grad_features = torch.zeros((B, C, N), dtype=torch.float32, device=grad_out.device)
+        grad_out_data = grad_out.detach().contiguous().float()
+        _cabi.call("apb_group_grad_f32", [grad_out_data, idx, grad_features, B, C, N, npoint, nsample],
+                   grad_out.device)
+        return grad_features, None
+
+
+grouping_operation = GroupingOperation.apply
+
+
+def torch_grouping_operation(features, idx):
+    """Pure-torch grouping kept for API parity (reference group.py:120-137)."""
+    all_idx = idx.reshape(idx.shape[0], -1)
+    all_idx = all_idx.unsqueeze(1).repeat(1, features.shape[1], 1)
+    grouped_features = features.gather(2, all_idx.long())
+    return grouped_features.reshape(idx.shape[0], features.shape[1], idx.shape[1], idx.shape[2])
+
+
+class ThreeNN(Function):
+    @staticmethod
+    def forward(ctx, unknown: torch.Tensor, known: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+        """unknown (B,n,3), known (B,m,3) -> (dist (B,n,3) [sqrt applied], idx (B,n,3) int32);
+        reference upsampling.py:11-33."""
+        _check(unknown, "unknown", torch.float32)
+        _check(known, "known", torch.float32)
+        B, N, _ = unknown.size()
+        m = known.size(1)
+        dist2 = torch.empty((B, N, 3), dtype=torch.float32, device=unknown.device)
+        idx = torch.empty((B, N, 3), dtype=torch.int32, device=unknown.device)
+        _cabi.call("apb_three_nn_f32", [unknown, known, dist2, idx, B, N, m], unknown.device)
+        ctx.mark_non_differentiable(idx)
+        return torch.sqrt(dist2), idx
+
+    @staticmethod
+    def backward(ctx, a=None, b=None):
+        return None, None
+
+
+three_nn = ThreeNN.apply
+
+
+class ThreeInterpolate(Function):
+    @staticmethod
+    @torch.amp.custom_fwd(device_type="cuda", cast_inputs=torch.float32)
+    def forward(ctx, features: torch.Tensor, idx: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
+        """features (B,C,m), idx (B,n,3) int32, weight (B,n,3) -> (B,C,n); upsampling.py:43-67."""
+        _check(features, "features", torch.float32)
+        _check(idx, "idx", torch.int32)
+        _check(weight, "weight", torch.float32)
+        B, c, m = features.size()
+        n = idx.size(1)
+        ctx.three_interpolate_for_backward = (idx, weight, m)
+        output = torch.empty((B, c, n), dtype=torch.float32, device=features.device)
+        _cabi.call("apb_three_interp_f32", [features, idx, weight, output, B, c, m, n], features.device)
+        return output
+
+    @staticmethod
+    @torch.amp.custom_bwd(device_type="cuda")
+    def backward(ctx, grad_out: torch.Tensor):
+        idx, weight, m = ctx.three_interpolate_for_backward
+        B, c, n = grad_out.size()
+        grad_features = torch.zeros((B, c, m), dtype=torch.float32, device=grad_out.device)
+        grad_out_data = grad_out.detach().contiguous().float()
+        _cabi.call("apb_three_interp_grad_f32", [grad_out_data, idx, weight, grad_features, B, c, n, m],
+                   grad_out.device)
+        return grad_features, None, None
+
+
+three_interpolate = ThreeInterpolate.apply
+
+
+def three_interpolation(unknown_xyz, known_xyz, know_feat):
+    """reference upsampling.py:92-102: inverse-distance weights over the 3 nearest known points."""
+    dist, idx = three_nn(unknown_xyz, known_xyz)
+    dist_recip = 1.0 / (dist + 1e-8)
+    norm = torch.sum(dist_recip, dim=2, keepdim=True)
+    weight = dist_recip / norm
+    return three_interpolate(know_feat, idx, weight)
+
+
+def fps(data, number):
+    """data (B,N,C>=3) -> (B,number,C) sampled rows; reference subsample.py:148-156."""
+    fps_idx = furthest_point_sample(data[:, :, :3].contiguous(), number)
+    return torch.gather(data, 1, fps_idx.unsqueeze(-1).long().expand(-1, -1, data.shape[-1]))
+
+
+@torch.no_grad()
+def knn_query(k: int, support: torch.Tensor, query: torch.Tensor, return_dist2: bool = False):
+    """k nearest support points of every query, ordered by (squared distance, index).
+    support (B,N,3), query (B,M,3) -> idx (B,M,k) int32 [, dist2 (B,M,k)].
+    Stands in for torch.cdist + topk in the reference's KNN module (group.py:12-28)."""
+    _check(support, "support", torch.float32)
+    _check(query, "query", torch.float32)
+    B, N, _ = support.size()
+    M = query.size(1)
+    idx = torch.empty((B, M, k), dtype=torch.int32, device=support.device)
+    d2 = torch.empty((B, M, k), dtype=torch.float32, device=support.device) if return_dist2 else None
+    _cabi.call("apb_knn_f32", [query, support, idx, d2, B, N, M, int(k)], support.device)
+    return (idx, d2) if return_dist2 else idx

@@ -1,0 +1,131 @@
+"""Op microbench sweep (BASELINE.json configs[2]): FPS / ball_query(r=0.1,K=32) / grouping / gather at
+B=32, N=1k..100k, npoint=N/4, ours vs the reference's CUDA kernels (oracle/_ref) on the same B200, with
+roofline fractions from the ALGORITHMIC work of BASELINE.md 2c.  Writes JSON lines to stdout / --out."""
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from adaptpoint_b200 import ops  # noqa: E402
+from adaptpoint_b200.synth import make_clouds  # noqa: E402
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p))["hbm_gbs"], "measured"
+    return 6650.0, "fallback"
+
+
+def timeit(fn, iters, warm=3, flush=None):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        if flush is not None:
+            flush.add_(1.0)
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        fn()
+        e.record()
+        torch.cuda.synchronize()
+        ts.append(s.elapsed_time(e))
+    ts.sort()
+    return ts[len(ts) // 2], ts[0]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--sizes", default="1024,2048,4096,8192,16384,32768,65536,100000")
+    ap.add_argument("--B", type=int, default=32)
+    ap.add_argument("--iters", type=int, default=5)
+    ap.add_argument("--no-ref", action="store_true")
+    ap.add_argument("--ops", default="fps,ball_query,group,group_grad,gather")
+    ap.add_argument("--out", default="")
+    args = ap.parse_args()
+    dev = torch.device("cuda:0")
+    hbm, src = peaks()
+    refcuda = None
+    if not args.no_ref:
+        from oracle import refcuda as rc
+        refcuda = rc if rc.available() else None
+    flush = torch.zeros(160 * 1024 * 1024 // 4, device=dev)  # > 126 MB L2
+    B = args.B
+    lines = []
+    for N in [int(s) for s in args.sizes.split(",")]:
+        M, K = N // 4, 32
+        xyz = make_clouds(B, N, "shell", seed=0).to(dev)
+        want = args.ops.split(",")
+        idx = ops.furthest_point_sample(xyz, M)
+        new_xyz = torch.gather(xyz, 1, idx.long().unsqueeze(-1).expand(-1, -1, 3)).contiguous()
+        nbr = ops.ball_query(0.1, K, xyz, new_xyz)
+
+        def emit(op, ms, ms_min, alg_bytes, ref_ms, extra=None):
+            d = {"op": op, "B": B, "N": N, "M": M, "K": K, "ms": round(ms, 4), "ms_min": round(ms_min, 4),
+                 "alg_GB": round(alg_bytes / 1e9, 4), "achieved_GBs": round(alg_bytes / 1e9 / (ms / 1e3), 1),
+                 "frac_hbm": round(alg_bytes / 1e9 / (ms / 1e3) / hbm, 3), "peak": hbm, "peak_src": src,
+                 "ref_cuda_ms": None if ref_ms is None else round(ref_ms, 4),
+                 "speedup_vs_ref_cuda": None if ref_ms is None else round(ref_ms / ms, 2)}
+            if extra:
+                d.update(extra)
+            lines.append(d)
+            print(json.dumps(d), flush=True)
+
+        if "fps" in want:
+            ms, mn = timeit(lambda: ops.furthest_point_sample(xyz, M), args.iters, flush=flush)
+            rms = None
+            if refcuda is not None:
+                rms, _ = timeit(lambda: refcuda.fps(xyz, M), max(2, args.iters // 2), warm=1)
+            emit("fps", ms, mn, 20.0 * B * N * (M - 1), rms, {"compulsory_GB": B * (12 * N + 4 * M) / 1e9})
+        if "ball_query" in want:
+            ms, mn = timeit(lambda: ops.ball_query(0.1, K, xyz, new_xyz), args.iters, flush=flush)
+            rms = None
+            if refcuda is not None:
+                rms, _ = timeit(lambda: refcuda.ball_query(0.1, K, xyz, new_xyz), max(2, args.iters // 2), warm=1)
+            emit("ball_query", ms, mn, 4.0 * B * (3 * N + 3 * M + M * K), rms,
+                 {"pairs_upper": B * M * N, "Tpairs_per_s_upper": round(B * M * N / (ms / 1e3) / 1e12, 3)})
+        for C in (3, 32, 128):
+            if C * B * M * K * 4 > 24e9:
+                continue
+            feat = torch.randn(B, C, N, device=dev)
+            if "group" in want:
+                ms, mn = timeit(lambda: ops.grouping_operation(feat, nbr), args.iters, flush=flush)
+                rms = None
+                if refcuda is not None:
+                    rms, _ = timeit(lambda: refcuda.group(feat, nbr), max(2, args.iters // 2), warm=1)
+                emit(f"group_C{C}", ms, mn, 4.0 * B * (C * N + M * K + C * M * K), rms)
+            if "group_grad" in want:
+                go = torch.randn(B, C, M, K, device=dev)
+                gp = torch.zeros(B, C, N, device=dev)
+                from adaptpoint_b200 import _cabi
+
+                def bwd():
+                    gp.zero_()
+                    _cabi.call("apb_group_grad_f32", [go, nbr, gp, B, C, N, M, K], dev)
+                ms, mn = timeit(bwd, args.iters, flush=flush)
+                rms = None
+                if refcuda is not None:
+                    rms, _ = timeit(lambda: refcuda.group_grad(go, nbr, N), max(2, args.iters // 2), warm=1)
+                emit(f"group_grad_C{C}", ms, mn, 4.0 * B * (C * M * K + M * K + C * N), rms)
+                del go, gp
+            if "gather" in want and C in (3, 128):
+                ms, mn = timeit(lambda: ops.gather_operation(feat, idx), args.iters, flush=flush)
+                rms = None
+                if refcuda is not None:
+                    rms, _ = timeit(lambda: refcuda.gather(feat, idx), max(2, args.iters // 2), warm=1)
+                emit(f"gather_C{C}", ms, mn, 4.0 * B * (2 * C * M + M), rms)
+            del feat
+    if args.out:
+        os.makedirs(os.path.dirname(args.out), exist_ok=True)
+        with open(args.out, "w") as f:
+            for d in lines:
+                f.write(json.dumps(d) + "\n")
+
+
+if __name__ == "__main__":
+    main()

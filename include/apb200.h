@@ -1,0 +1,95 @@
+/*
+ * apb200.h -- C-ABI of libapb200.so: hand-written sm_100a CUDA kernels for the PointNeXt
+ * set-abstraction hot path of AdaptPoint/OpenPoints.
+ *
+ * Drop-in boundary: each entry point replaces one function of the reference's pybind module
+ * `pointnet2_batch_cuda` (openpoints/cpp/pointnet2_batch/src/pointnet2_api.cpp:10-24); the
+ * reference wrapper it stands in for is cited per function.  Differences from the reference ABI,
+ * all deliberate:
+ *   - plain device pointers + int sizes instead of at::Tensor;
+ *   - an explicit cudaStream_t (passed as void*) instead of the legacy default stream;
+ *   - an int status is returned (0 = ok, otherwise a cudaError_t or APB_E_*); nothing calls
+ *     exit() (the reference launchers fprintf + exit(-1), e.g. sampling_gpu.cu:46-50);
+ *   - the current CUDA device of the calling thread is used (caller sets it, as torch does).
+ * Ownership is unchanged: the caller allocates every buffer, pre-zeroes gradient accumulators and
+ * the ball-query index buffer exactly as the reference Python does, the callee keeps no state.
+ * Layouts are the reference's: coordinates (B,N,3) point-major f32, features (B,C,N)
+ * channel-major f32, indices int32, all dense/contiguous.
+ */
+#ifndef APB200_H_
+#define APB200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void *apb_stream_t; /* a cudaStream_t */
+
+#define APB_OK 0
+#define APB_E_INVALID 10001     /* bad argument (null pointer, negative size, unsupported shape) */
+#define APB_E_UNSUPPORTED 10002 /* shape outside what the kernel family covers */
+
+/* Library / build identification: "apb200 <version> sm_100a". */
+const char *apb_version(void);
+/* Human-readable text for a status returned by any apb_* call. */
+const char *apb_error_string(int status);
+
+/* The reference's FPS thread-block size rule, cuda_utils.h:10-14 (opt_n_threads). It fixes the
+ * tie-break order of apb_fps_f32. */
+int apb_fps_block_size(int n);
+
+/* furthest_point_sampling_wrapper(b,n,m,points,temp,idx)   -- sampling.cpp:39-48,
+ * kernel sampling_gpu.cu:100-216.
+ *   xyz  (B,N,3) f32;  idx (B,m) int32 out;
+ *   temp (B,N) f32 or NULL: if given it is the initial running min-distance (the reference Python
+ *        fills 1e10, subsample.py:94) and receives the final one, as in the reference; if NULL
+ *        1e10 is assumed and nothing is written back.
+ * Indices are bit-identical to the reference kernel, including its tie rule (smallest
+ * bit-reversed (k mod block_size), then smallest k). */
+int apb_fps_f32(const float *xyz, float *temp, int32_t *idx, int B, int N, int m, apb_stream_t stream);
+
+/* gather_points_wrapper(b,c,n,npoints,points,idx,out)      -- sampling.cpp:11-22 */
+int apb_gather_f32(const float *points, const int32_t *idx, float *out, int B, int C, int N, int m,
+                   apb_stream_t stream);
+/* gather_points_grad_wrapper(b,c,n,npoints,grad_out,idx,grad_points) -- sampling.cpp:25-36;
+ * grad_points (B,C,N) must be pre-zeroed (accumulated into). */
+int apb_gather_grad_f32(const float *grad_out, const int32_t *idx, float *grad_points, int B, int C,
+                        int N, int m, apb_stream_t stream);
+
+/* ball_query_wrapper(b,n,m,radius,nsample,new_xyz,xyz,idx) -- ball_query.cpp:29-39,
+ * kernel ball_query_gpu.cu:15-51.  idx (B,M,K) is fully written (queries without a hit get
+ * zeros, which is what the reference's pre-zeroed buffer holds). */
+int apb_ball_query_f32(const float *new_xyz, const float *xyz, int32_t *idx, int B, int N, int M,
+                       float radius, int nsample, apb_stream_t stream);
+
+/* kNN over squared distances, order (distance, index) ascending.  Replaces KNN.forward =
+ * torch.cdist + topk in group.py:12-28 (no native function in the reference).
+ * idx (B,M,K) int32; dist2 (B,M,K) f32 or NULL. K <= 128. */
+int apb_knn_f32(const float *new_xyz, const float *xyz, int32_t *idx, float *dist2, int B, int N, int M,
+                int K, apb_stream_t stream);
+
+/* group_points_wrapper(b,c,n,npoints,nsample,points,idx,out) -- group_points.cpp:25-35 */
+int apb_group_f32(const float *points, const int32_t *idx, float *out, int B, int C, int N, int M, int K,
+                  apb_stream_t stream);
+/* group_points_grad_wrapper(b,c,n,npoints,nsample,grad_out,idx,grad_points) -- group_points.cpp:11-22;
+ * grad_points (B,C,N) pre-zeroed. */
+int apb_group_grad_f32(const float *grad_out, const int32_t *idx, float *grad_points, int B, int C, int N,
+                       int M, int K, apb_stream_t stream);
+
+/* three_nn_wrapper(b,n,m,unknown,known,dist2,idx)          -- interpolate.cpp:17-27 */
+int apb_three_nn_f32(const float *unknown, const float *known, float *dist2, int32_t *idx, int B, int n,
+                     int m, apb_stream_t stream);
+/* three_interpolate_wrapper(b,c,m,n,points,idx,weight,out) -- interpolate.cpp:30-42 */
+int apb_three_interp_f32(const float *points, const int32_t *idx, const float *weight, float *out, int B,
+                         int C, int m, int n, apb_stream_t stream);
+/* three_interpolate_grad_wrapper(b,c,n,m,grad_out,idx,weight,grad_points) -- interpolate.cpp:45-57;
+ * grad_points (B,C,m) pre-zeroed. */
+int apb_three_interp_grad_f32(const float *grad_out, const int32_t *idx, const float *weight,
+                              float *grad_points, int B, int C, int n, int m, apb_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* APB200_H_ */
