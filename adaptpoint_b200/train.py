@@ -1,0 +1,167 @@
+"""One AdaptPoint training step: imitator (generator) + discriminator update, then the classifier update.
+
+Host-side mirror of the two hot loops of the reference
+  train_gan        examples/classification/train_autoaug.py:119-237   (per-iteration body :131-207)
+  train_one_epoch  examples/classification/train_autoaug.py:463-523   (per-iteration body :474-506)
+  get_gan_model    examples/classification/train_autoaug.py:80-117    (Adam lr 1e-4 / 4e-4, betas .5/.999, BCE)
+  get_feedback_loss_ver1  openpoints/function_adaptpoint/ganloss_cls.py:31-65
+with the reference's config values from cfgs/scanobjectnn/pointnext-s_adaptpoint_1.yaml:38-74 and
+cfgs/scanobjectnn/default.yaml:35-52.  Deliberate differences:
+  * generated clouds stay on the device (the reference copies three (B,N,.) arrays to host numpy every
+    iteration and rebuilds a DataLoader per epoch);
+  * data parallelism is explicit: per-rank batch fixed, gradients of every updated network are averaged with
+    ONE flat NCCL all-reduce per optimizer step (the reference wraps in DDP but calls `model.module....`, so
+    its reducer never fires), BatchNorm becomes SyncBatchNorm when world_size > 1 like the reference
+    (main.py:27);
+  * logging / TensorBoard / h5 dumps are left out.
+"""
+import copy
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+from . import ops
+from .imitator import AdaptPoint_Augmentor, PointDiscriminator1, PointWOLF_classversion
+from .models import SmoothCrossEntropy, build_model
+
+ADAPTPOINT_CFG = dict(
+    model="pointnext-s", num_points=1024, num_classes=15, in_channels=4, batch_size=32, loader_points=2048,
+    lr=0.002, weight_decay=0.05, grad_norm_clip=10.0, label_smoothing=0.3, epochs=300,
+    pointwolf=dict(w_num_anchor=4, w_sigma=0.5, w_R_range=10, w_S_range=3, w_T_range=0.25),
+    adaptmodel_gan=dict(w_num_anchor=4, w_sigma=0.5, w_R_range=10, w_S_range=3, w_T_range=0.25),
+    adaptmodel_dis=dict(num_classes=15, normal_channel=False),
+    adaptpoint_params=dict(lr_generator=1e-4, lr_discriminator=4e-4, b1=0.5, b2=0.999, hardratio_s=3, hardratio=3),
+    feedbackloss_ratio=1,
+)
+
+
+def _world():
+    return dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+
+
+def allreduce_grads(params, bucket=None):
+    """Average gradients over ranks with one flat all-reduce (NCCL over NVLink on the GPU box, gloo in tests)."""
+    world = _world()
+    if world == 1:
+        return
+    grads = [p.grad for p in params if p.grad is not None]
+    if not grads:
+        return
+    flat = torch._utils._flatten_dense_tensors(grads)
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM)
+    flat.div_(world)
+    for g, s in zip(grads, torch._utils._unflatten_dense_tensors(flat, grads)):
+        g.copy_(s)
+
+
+def feedback_loss(classifier, criterion, data_real, data_fake, epoch, cfg):
+    """|1 - exp(L_fake - rho * L_real)| with the classifier in eval mode but inside autograd
+    (ganloss_cls.py:31-65)."""
+    classifier.eval()
+    pred_fake = classifier(data_fake)
+    pred_real = classifier(data_real)
+    label = data_real["y"].long()
+    loss_fake, loss_real = criterion(pred_fake, label), criterion(pred_real, label)
+    ap = cfg["adaptpoint_params"]
+    rho = ap["hardratio_s"] + (ap["hardratio"] - ap["hardratio_s"]) * epoch / cfg["epochs"]
+    return torch.abs(1 - torch.exp(loss_fake - rho * loss_real)).mean()
+
+
+class AdaptPointTrainer:
+    """Holds classifier / imitator / discriminator + their optimizers; `step(batch)` = one train_gan iteration
+    followed by one train_one_epoch iteration on the generated batch."""
+
+    def __init__(self, cfg=None, device="cuda", fused_eval=False, seed=0):
+        self.cfg = copy.deepcopy(ADAPTPOINT_CFG if cfg is None else cfg)
+        self.device = torch.device(device)
+        torch.manual_seed(seed)
+        self.classifier = build_model(self.cfg["model"], fused=fused_eval).to(self.device)
+        self.generator = AdaptPoint_Augmentor(**self.cfg["adaptmodel_gan"]).to(self.device)
+        self.discriminator = PointDiscriminator1(**self.cfg["adaptmodel_dis"]).to(self.device)
+        if _world() > 1:
+            self.classifier = nn.SyncBatchNorm.convert_sync_batchnorm(self.classifier)
+            self.generator = nn.SyncBatchNorm.convert_sync_batchnorm(self.generator)
+            for net in (self.classifier, self.generator, self.discriminator):      # same init on every rank
+                for t in list(net.parameters()) + list(net.buffers()):
+                    dist.broadcast(t.data, 0)
+        ap = self.cfg["adaptpoint_params"]
+        self.opt_c = torch.optim.AdamW(self.classifier.parameters(), lr=self.cfg["lr"],
+                                       weight_decay=self.cfg["weight_decay"])
+        self.opt_g = torch.optim.Adam(self.generator.parameters(), lr=ap["lr_generator"], betas=(ap["b1"], ap["b2"]))
+        self.opt_d = torch.optim.Adam(self.discriminator.parameters(), lr=ap["lr_discriminator"],
+                                      betas=(ap["b1"], ap["b2"]))
+        self.criterion_gan = nn.BCELoss()
+        self.criterion = SmoothCrossEntropy(label_smoothing=self.cfg["label_smoothing"])
+        self.pointwolf = PointWOLF_classversion(**self.cfg["pointwolf"])
+        self.epoch = 0
+
+    # -- train_autoaug.py:131-207 ---------------------------------------------------------------------------
+    def gan_iteration(self, points, label):
+        """points (B,N,C>=4) loader-shaped, label (B,).  Returns (generated batch (B,N,C), g_loss, d_loss)."""
+        cfg = self.cfg
+        G, D, C = self.generator, self.discriminator, self.classifier
+        G.train(); D.train(); C.eval()
+        points_clone = points.clone()
+        inp = points[:, :, :3].contiguous()
+        self.pointwolf(inp)                                     # the reference runs it for its h5 dump (:143)
+        B = inp.size(0)
+        real_label = torch.full((B, 1), 0.9, device=inp.device)
+        fake_label = torch.full((B, 1), 0.1, device=inp.device)
+
+        _, gen = G(inp)
+        g_loss_raw = self.criterion_gan(D(gen), real_label)
+        fake_pts = torch.cat([gen, points[:, :, 3:]], dim=-1)   # `points[:, :, :3] = gen_imgs` (:152)
+        nc = cfg["in_channels"]
+        data_fake = {"pos": fake_pts[:, :, :3].contiguous(), "y": label,
+                     "x": fake_pts[:, :, :nc].transpose(1, 2).contiguous()}
+        data_real = {"pos": points_clone[:, :, :3].contiguous(), "y": label,
+                     "x": points_clone[:, :, :nc].transpose(1, 2).contiguous()}
+        ratio = cfg.get("feedbackloss_ratio", 1)
+        g_loss = g_loss_raw
+        if ratio > 0:
+            g_loss = g_loss_raw + feedback_loss(C, self.criterion, data_real, data_fake, self.epoch, cfg) * ratio
+        self.opt_g.zero_grad()
+        g_loss.backward()
+        allreduce_grads(list(G.parameters()))
+        self.opt_g.step()
+
+        real_loss = self.criterion_gan(D(inp), real_label)
+        fake_loss = self.criterion_gan(D(gen.detach()), fake_label)
+        d_loss = (real_loss + fake_loss) / 2
+        self.opt_d.zero_grad()
+        d_loss.backward()
+        allreduce_grads(list(D.parameters()))
+        self.opt_d.step()
+        C.zero_grad(set_to_none=True)                           # model_pointcloud.zero_grad() (:232)
+        return fake_pts.detach(), g_loss.detach(), d_loss.detach()
+
+    # -- train_autoaug.py:474-506 ---------------------------------------------------------------------------
+    def classifier_iteration(self, points, target):
+        cfg = self.cfg
+        model = self.classifier
+        model.train()
+        npoints = cfg["num_points"]
+        if points.shape[1] > npoints:                           # point resampling strategy (:485-499)
+            point_all = {1024: 1200, 4096: 4800, 8192: 8192}[npoints]
+            point_all = min(point_all, points.size(1))
+            fps_idx = ops.furthest_point_sample(points[:, :, :3].contiguous(), point_all)
+            keep = torch.randperm(point_all)[:npoints].to(points.device)  # np.random.choice(point_all, npoints, False)
+            fps_idx = fps_idx[:, keep]
+            points = torch.gather(points, 1, fps_idx.unsqueeze(-1).long().expand(-1, -1, points.shape[-1]))
+        data = {"pos": points[:, :, :3].contiguous(),
+                "x": points[:, :, :cfg["in_channels"]].transpose(1, 2).contiguous()}
+        logits, loss = model.get_logits_loss(data, target)
+        loss.backward()
+        allreduce_grads(list(model.parameters()))
+        if cfg.get("grad_norm_clip"):
+            torch.nn.utils.clip_grad_norm_(model.parameters(), cfg["grad_norm_clip"], norm_type=2)
+        self.opt_c.step()
+        model.zero_grad()
+        return logits.detach(), loss.detach()
+
+    def step(self, points, label):
+        """One full AdaptPoint step on a loader-shaped batch.  Returns (cls_loss, g_loss, d_loss) tensors."""
+        fake, g_loss, d_loss = self.gan_iteration(points, label)
+        _, loss = self.classifier_iteration(fake, label)
+        return loss, g_loss, d_loss

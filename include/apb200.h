@@ -89,6 +89,22 @@ int apb_three_interp_f32(const float *points, const int32_t *idx, const float *w
 int apb_three_interp_grad_f32(const float *grad_out, const int32_t *idx, const float *weight,
                               float *grad_points, int B, int C, int n, int m, apb_stream_t stream);
 
+/* Fused AdaptPoint / PointWOLF deformation (no native function in the reference: replaces the torch op chain of
+ * AdaptPoint_Augmentor.forward, generator_component4_15.py:148-173 + 204-234 + 294 + 313-327, and
+ * PointWOLF_classversion.__call__, online_aug/pointwolf.py:27-178).
+ *   xyz (B,N,3); anchor (B,M,3) = xyz[fps idx]; affine (B,M,12) = row-major A_m = R_m S_m (9) then trl_m (3);
+ *   proj_axis (B,3) in {0,1}; mask (B,N) or NULL; sigma > 0; M <= 8.
+ *   out (B,N,3) = mask * s * (q - mean q),  q = kernel regression of the M local transforms (see deform.cu);
+ *   stats (B,8) or NULL: mean xyz, s, max norm r*, argmax n* (int bits) -- consumed by the backward. */
+int apb_deform_mask_fwd_f32(const float *xyz, const float *anchor, const float *affine, const float *proj_axis,
+                            const float *mask, float sigma, float *out, float *stats, int B, int N, int M,
+                            apb_stream_t stream);
+/* Backward of the above w.r.t. affine (grad_affine (B,M,12), fully written) and mask (grad_mask (B,N) or NULL).
+ * xyz / anchor are data in the reference's loop (train_autoaug.py:136-148) and get no gradient. */
+int apb_deform_mask_bwd_f32(const float *xyz, const float *anchor, const float *affine, const float *proj_axis,
+                            const float *mask, float sigma, const float *stats, const float *grad_out,
+                            float *grad_affine, float *grad_mask, int B, int N, int M, apb_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

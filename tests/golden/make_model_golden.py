@@ -1,0 +1,161 @@
+"""Generates tests/golden/model_*.npz by running the REFERENCE's own Python modules (loaded by ref_loader.py
+from /root/reference, CPU, native ops served by the C oracle) on seeded inputs and deterministic parameters
+(fill.py).  Run in the build container:  python tests/golden/make_model_golden.py
+Each case is self-checked here against our modules run on the CPU stand-in ops (oracle/torch_ops.py); the
+committed fixtures are then used by tests/test_models_cpu.py (CPU) and tests/test_models_gpu.py (CUDA kernels).
+"""
+import copy
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE)
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+import ref_loader  # noqa: E402
+from fill import fill_state  # noqa: E402
+from adaptpoint_b200.synth import make_clouds  # noqa: E402
+
+
+def batch(B, N, seed, kind="shell"):
+    pos = make_clouds(B, N, kind, seed)
+    h = pos[:, :, 1:2] - pos[:, :, 1:2].amin(dim=1, keepdim=True)
+    x = torch.cat([pos, h], -1).transpose(1, 2).contiguous()
+    y = torch.randint(0, 15, (B,), generator=torch.Generator().manual_seed(seed + 1))
+    return pos, x, y
+
+
+def train_no_dropout(m):
+    """train mode (BatchNorm batch statistics) with Dropout disabled: its draws are device-specific."""
+    m.train()
+    for sub in m.modules():
+        if isinstance(sub, torch.nn.Dropout):
+            sub.eval()
+
+
+def grads_summary(model, names):
+    sd = dict(model.named_parameters())
+    return {f"grad::{n}": sd[n].grad.detach().numpy().copy() for n in names}
+
+
+def save(name, **arrays):
+    path = os.path.join(HERE, f"model_{name}.npz")
+    np.savez_compressed(path, **{k: np.asarray(v) for k, v in arrays.items()})
+    print("wrote", path, {k: np.asarray(v).shape for k, v in arrays.items()})
+
+
+def main():
+    R = ref_loader.load_reference()
+    E = R.EasyDict
+    from adaptpoint_b200.models import CONFIGS
+
+    # ---- PointNeXt-S classification (cfgs/scanobjectnn/pointnext-s.yaml) -----------------------------------
+    cfg = copy.deepcopy(CONFIGS["pointnext-s"])
+    cfg.pop("kind")
+    cfg["NAME"] = "BaseCls"
+    ref = R.build_model_from_cfg(E(cfg))
+    names = fill_state(ref, 0)
+    B, N = 3, 512
+    pos, x, y = batch(B, N, 11)
+    ref.eval()
+    with torch.no_grad():
+        logits_eval = ref({"pos": pos, "x": x})
+    train_no_dropout(ref)
+    pos_g = pos.clone().requires_grad_(True)
+    x_g = x.clone().requires_grad_(True)
+    logits_tr, loss = ref.get_logits_loss({"pos": pos_g, "x": x_g}, y)
+    loss.backward()
+    gnames = ["encoder.encoder.0.0.convs.0.0.weight", "encoder.encoder.1.0.convs.0.0.weight",
+              "encoder.encoder.2.0.skipconv.0.weight", "encoder.encoder.4.0.convs.1.1.weight",
+              "prediction.head.0.0.weight"]
+    save("cls_s", B=B, N=N, seed=11, logits_eval=logits_eval.numpy(), logits_train=logits_tr.detach().numpy(),
+         loss=loss.item(), grad_pos=pos_g.grad.numpy(), grad_x=x_g.grad.numpy(),
+         param_names=np.array([n for n, _ in names]), **grads_summary(ref, gnames))
+
+    # ---- PointNeXt-B segmentation (encoder + FeaturePropogation decoder + SegHead) --------------------------
+    cfg = copy.deepcopy(CONFIGS["pointnext-b-seg"])
+    cfg.pop("kind")
+    cfg["NAME"] = "BaseSeg"
+    cfg["decoder_args"]["NAME"] = "PointNextDecoder"
+    ref = R.build_model_from_cfg(E(cfg))
+    names = fill_state(ref, 1)
+    B, N = 2, 1024
+    pos, x, _ = batch(B, N, 12, "ball")
+    ref.eval()
+    with torch.no_grad():
+        seg_eval = ref({"pos": pos, "x": x})
+    train_no_dropout(ref)
+    x_g = x.clone().requires_grad_(True)
+    out = ref({"pos": pos, "x": x_g})
+    tgt = torch.randint(0, 13, (B, N), generator=torch.Generator().manual_seed(5))
+    loss = torch.nn.functional.cross_entropy(out, tgt)
+    loss.backward()
+    gnames = ["encoder.encoder.1.1.convs.convs.0.0.weight", "encoder.encoder.2.2.pwconv.1.0.weight",
+              "decoder.decoder.0.0.convs.0.0.weight", "head.head.0.0.weight"]
+    save("seg_b", B=B, N=N, seed=12, seg_eval=seg_eval.numpy(), seg_train=out.detach().numpy(), loss=loss.item(),
+         grad_x=x_g.grad.numpy(), param_names=np.array([n for n, _ in names]), **grads_summary(ref, gnames))
+
+    # ---- groupers -----------------------------------------------------------------------------------------
+    pos, x, _ = batch(2, 600, 13, "ball")
+    fidx = R.subsample.furthest_point_sample(pos, 150).long()
+    q = torch.gather(pos, 1, fidx.unsqueeze(-1).expand(-1, -1, 3)).contiguous()
+    qg = R.group.QueryAndGroup(0.2, 16, normalize_dp=True)
+    dp, fj = qg(q, pos, x)
+    kg = R.group.KNNGroup(12, normalize_dp=True)
+    kdp, kfj = kg(q, pos, x)
+    save("groupers", seed=13, qg_dp=dp.numpy(), qg_fj=fj.numpy(), knn_dp=kdp.numpy(), knn_fj=kfj.numpy())
+
+    # ---- AdaptPoint imitator ------------------------------------------------------------------------------
+    gen = R.AdaptPoint_Augmentor(w_num_anchor=4, w_sigma=0.5, w_R_range=10, w_S_range=3, w_T_range=0.25)
+    names = fill_state(gen, 2)
+    B, N, M = 2, 512, 4
+    pos, _, _ = batch(B, N, 14)
+    gen.train()
+    S = 1234
+    torch.manual_seed(S)                                   # replicate the reference's draws to record them
+    gumbel = -torch.empty(B, N, 2).exponential_().log()
+    a = torch.Tensor(B, M, 3).uniform_(0, 1)
+    dropout = torch.bernoulli(a)
+    axis = ((torch.randint(1, 8, (B, M))[:, :, None] & (1 << torch.arange(3))) > 0).int()
+    proj = ((torch.randint(1, 8, (B, 1))[:, :, None] & (1 << torch.arange(3))) > 0).int()
+    torch.manual_seed(S)
+    _, xyz_new = gen(pos)
+    w = torch.randn(B, N, 3, generator=torch.Generator().manual_seed(3))
+    (xyz_new * w).sum().backward()
+    gnames = ["predict_prob_layer.embedding.net.0.weight", "predict_prob_layer.head.prob_head.0.weight",
+              "predict_prob_layer.fuse_masking.0.weight", "predict_prob_layer.pointset_grouper_list.1.affine_alpha",
+              "predict_prob_layer.decode_list.3.fuse.net.0.weight"]
+    save("generator", B=B, N=N, seed=14, gumbel=gumbel.numpy(), dropout=dropout.numpy(), axis=axis.numpy(),
+         proj_axis=proj.numpy(), xyz_new=xyz_new.detach().numpy(), w=w.numpy(),
+         param_names=np.array([n for n, _ in names]), **grads_summary(gen, gnames))
+
+    # ---- discriminator (eval: no dropout, no power iteration) ---------------------------------------------
+    dis = R.PointDiscriminator1(num_classes=15, normal_channel=False)
+    names = fill_state(dis, 3)
+    dis.eval()
+    pos_g = pos.clone().requires_grad_(True)
+    prob = dis(pos_g)
+    prob.sum().backward()
+    save("discriminator", seed=14, prob=prob.detach().numpy(), grad_pos=pos_g.grad.numpy(),
+         param_names=np.array([n for n, _ in names]))
+
+    # ---- PointWOLF ----------------------------------------------------------------------------------------
+    wolf = R.PointWOLF_classversion(w_num_anchor=4, w_sigma=0.5, w_R_range=10, w_S_range=3, w_T_range=0.25)
+    torch.manual_seed(S)
+    a = torch.Tensor(B, M, 3).uniform_(0, 1)
+    dropout = torch.bernoulli(a)
+    axis = ((torch.randint(1, 8, (B, M))[:, :, None] & (1 << torch.arange(3))) > 0).int()
+    r = torch.FloatTensor(B, M, 3).uniform_(-10, 10)
+    s = torch.FloatTensor(B, M, 3).uniform_(1., 3)
+    t = torch.FloatTensor(B, M, 3).uniform_(-0.25, 0.25)
+    proj = ((torch.randint(1, 8, (B, 1))[:, :, None] & (1 << torch.arange(3))) > 0).int()
+    torch.manual_seed(S)
+    _, wolf_out = wolf(pos)
+    save("pointwolf", seed=14, dropout=dropout.numpy(), axis=axis.numpy(), R=r.numpy(), S=s.numpy(), T=t.numpy(),
+         proj_axis=proj.numpy(), out=wolf_out.numpy())
+
+
+if __name__ == "__main__":
+    main()
