@@ -81,12 +81,28 @@ def _ptr(t):
     return ctypes.c_void_p(t.data_ptr())
 
 
+# Launch accounting for bench.py: LAUNCHES counts C-ABI calls (one kernel launch each); when TRACE is a list,
+# every call is bracketed by CUDA events on the launching stream: (name, int args, start event, end event).
+LAUNCHES = 0
+TRACE = None
+
+
 def call(name, tensors_and_scalars, device):
     """Invoke one C-ABI entry point on `device`'s current stream and raise on a non-zero status."""
+    global LAUNCHES
     lib = load()
     with torch.cuda.device(device):
-        stream = ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+        ts = torch.cuda.current_stream(device)
+        stream = ctypes.c_void_p(ts.cuda_stream)
         args = [(_ptr(a) if (a is None or isinstance(a, torch.Tensor)) else a) for a in tensors_and_scalars]
-        status = getattr(lib, name)(*args, stream)
+        LAUNCHES += 1
+        if TRACE is not None:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(ts)
+            status = getattr(lib, name)(*args, stream)
+            e1.record(ts)
+            TRACE.append((name, tuple(a for a in tensors_and_scalars if isinstance(a, int)), e0, e1))
+        else:
+            status = getattr(lib, name)(*args, stream)
     if status != 0:
         raise ApbError(f"{name} failed: {lib.apb_error_string(status).decode()} (status {status})")

@@ -1,0 +1,322 @@
+#!/usr/bin/env python
+"""bench.py -- the driver's measurement contract for adaptpoint_b200.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+  (N>1: launched by `python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...`)
+
+Workload (BASELINE.json configs[1]): one full AdaptPoint training step of
+cfgs/scanobjectnn/pointnext-s_adaptpoint_1.yaml -- imitator (deformation + mask controllers) + discriminator
+update, then the PointNeXt-S classifier update on the generated batch -- on a synthetic ScanObjectNN-C-shaped
+loader batch (B=32 per GPU, 2048 points, xyz+height, 15 classes).  A "step" = adaptpoint_b200.train.
+AdaptPointTrainer.step on one batch.  Metric: training samples/s, whole job (weak scaling: per-GPU batch fixed).
+
+  value      : inputs already resident in HBM, per-step CUDA events, max over ranks.
+  e2e        : same step through the public API from PINNED HOST buffers: H2D of the batch and D2H of the three
+               losses inside the timed region every step.
+  roofline   : the dominant kernel OF OURS inside the timed region (CUDA events around every C-ABI launch),
+               algorithmic bytes per launch (DESIGN.md / SURVEY.md 8d) / its average duration vs the measured HBM
+               peak of MEASURED_PEAKS.json.
+  cpu_baseline / --impl reference : the same step through the pure-PyTorch CPU equivalents of the ops
+               (oracle/torch_ops.py, test infrastructure) on the box's host cores, on a bounded sample.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = "adaptpoint_pointnext_s_train_samples_per_s"
+UNIT = "samples/s"
+WORKLOAD = "pointnext-s_adaptpoint_1 full step (imitator+discriminator+classifier), B=32/GPU, N=2048, 15 classes"
+B_PER_GPU, N_POINTS = 32, 2048
+
+
+def loader_batch(B, N, seed):
+    """Synthetic ScanObjectNN-C-shaped loader batch: x (B,N,4) = unit-ball xyz + height, y (B,)."""
+    from adaptpoint_b200.synth import make_clouds
+    pos = make_clouds(B, N, "shell", seed)
+    h = pos[:, :, 1:2] - pos[:, :, 1:2].amin(dim=1, keepdim=True)
+    y = torch.randint(0, 15, (B,), generator=torch.Generator().manual_seed(seed + 999))
+    return torch.cat([pos, h], -1).contiguous(), y
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d["hbm_gbs"], "measured (MEASURED_PEAKS.json, burst copy)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# algorithmic bytes per launch (SURVEY.md 8d / DESIGN.md "Kernels")
+# ---------------------------------------------------------------------------------------------------------------
+def alg_bytes(name, a):
+    if name == "apb_fps_f32":
+        B, N, m = a
+        return 20.0 * B * N * max(m - 1, 0)
+    if name == "apb_ball_query_f32":
+        B, N, M, K = a
+        return 4.0 * B * (3 * N + 3 * M + M * K)
+    if name == "apb_knn_f32":
+        B, N, M, K = a
+        return 4.0 * B * (3 * N + 3 * M + 2 * M * K)
+    if name in ("apb_group_f32", "apb_group_grad_f32"):
+        B, C, N, M, K = a
+        return 4.0 * B * (C * N + M * K + C * M * K)
+    if name in ("apb_gather_f32", "apb_gather_grad_f32"):
+        B, C, N, m = a
+        return 4.0 * B * (2 * C * m + m)
+    if name == "apb_three_nn_f32":
+        B, n, m = a
+        return 4.0 * B * (3 * n + 3 * m + 6 * n)
+    if name in ("apb_three_interp_f32", "apb_three_interp_grad_f32"):
+        B, C, x, y = a
+        m, n = (x, y) if name == "apb_three_interp_f32" else (y, x)
+        return 4.0 * B * (C * m + 6 * n + C * n)
+    if name == "apb_deform_mask_fwd_f32":
+        B, N, M = a
+        return 4.0 * B * (3 * N + N + 3 * N)
+    if name == "apb_deform_mask_bwd_f32":
+        B, N, M = a
+        return 4.0 * B * (3 * N + N + 3 * N + N)
+    if name.startswith("apb_sa_fused"):
+        return None
+    return None
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except Exception:
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# CPU arm (cpu_baseline leg and --impl reference): oracle-side code only
+# ---------------------------------------------------------------------------------------------------------------
+def cpu_step_rate(sample_B, steps, warmup):
+    """The AdaptPoint step on host cores through the pure-PyTorch op equivalents; returns (samples/s, cores)."""
+    from oracle import torch_ops
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    with torch_ops.patched(pure_torch=True):
+        from adaptpoint_b200.train import AdaptPointTrainer
+        tr = AdaptPointTrainer(device="cpu", seed=0)
+        pts, y = loader_batch(sample_B, N_POINTS, 0)
+        for _ in range(warmup):
+            tr.step(pts.clone(), y)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            tr.step(pts.clone(), y)
+        dt = time.perf_counter() - t0
+    return sample_B * steps / dt, cores, dt / steps
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sample_B = 4
+    v, cores, per = cpu_step_rate(sample_B, max(1, args.steps), max(1, min(args.warmup, 1)))
+    sample = f"{sample_B} of the {B_PER_GPU} clouds per step (N={N_POINTS}), {args.steps} steps, torch CPU threads={cores}"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": round(v, 3), "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(per * 1e3, 2), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "arm": "pure-PyTorch CPU equivalents of the pointnet2_batch ops under the "
+                   "same module definitions (oracle/torch_ops.py); the reference's CUDA-only extension has no CPU path"},
+        "cpu_baseline": {"value": round(v, 3), "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": round(v, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch.distributed as dist
+    from adaptpoint_b200 import _cabi
+    from adaptpoint_b200.train import AdaptPointTrainer
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (adaptpoint_b200 has no CPU product path)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    torch.backends.cudnn.allow_tf32 = False            # strict fp32 in the library GEMMs/convs ("dtype": "f32")
+    torch.backends.cuda.matmul.allow_tf32 = False
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _cabi.load()
+
+    tr = AdaptPointTrainer(device=dev, seed=0)
+    pts_h, y_h = loader_batch(B_PER_GPU, N_POINTS, 100 + rank)
+    pts_pin, y_pin = pts_h.pin_memory(), y_h.pin_memory()
+    loss_pin = torch.empty(3, dtype=torch.float32).pin_memory()
+    pts_d, y_d = pts_h.to(dev), y_h.to(dev)
+    flush = torch.empty(256 * 1024 * 1024 // 4, device=dev)          # > 126 MB L2
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(step_fn, steps):
+        """per-step CUDA events with an L2 flush between steps (outside the event pairs); returns total ms."""
+        evs = []
+        barrier()
+        for _ in range(steps):
+            flush.add_(1.0)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            step_fn()
+            e1.record()
+            evs.append((e0, e1))
+        barrier()
+        return sum(a.elapsed_time(b) for a, b in evs)
+
+    def resident_step():
+        tr.step(pts_d.clone(), y_d)
+
+    def e2e_step():
+        p = pts_pin.to(dev, non_blocking=True)
+        y = y_pin.to(dev, non_blocking=True)
+        losses = tr.step(p, y)
+        loss_pin.copy_(torch.stack([l.float() for l in losses]), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        resident_step()
+    e2e_step()
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    _cabi.LAUNCHES = 0
+    _cabi.TRACE = []
+    ms_total = timed(resident_step, args.steps)
+    launches = _cabi.LAUNCHES
+    trace, _cabi.TRACE = _cabi.TRACE, None
+    ms_e2e = timed(e2e_step, args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+
+    t = torch.tensor([ms_total, ms_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total, ms_e2e = t.tolist()
+
+    if rank == 0:
+        hbm, peak_src = peaks()
+        agg = {}
+        for name, a, e0, e1 in trace:
+            d = agg.setdefault((name, a), [0, 0.0])
+            d[0] += 1
+            d[1] += e0.elapsed_time(e1)
+        ours_ms = sum(v[1] for v in agg.values())
+        table = sorted(((k, v) for k, v in agg.items()), key=lambda kv: -kv[1][1])
+        (dname, dargs), (dcount, dms) = table[0]
+        ab = alg_bytes(dname, dargs)
+        avg_s = dms / dcount / 1e3
+        achieved = ab / 1e9 / avg_s if ab else None
+        kern = [{"call": k[0], "dims": list(k[1]), "launches": v[0], "ms_total": round(v[1], 3),
+                 "share_of_step": round(v[1] / ms_total, 4)} for k, v in table[:8]]
+        samples = world * B_PER_GPU * args.steps
+        out = {
+            "metric": METRIC, "value": round(samples / (ms_total / 1e3), 2), "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms_total / args.steps, 3),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "global_batch": world * B_PER_GPU, "parallelism": f"dp{world}",
+                       "l2": "256 MB flush write between timed steps (outside the per-step event pairs)",
+                       "timing": "per-step CUDA events on the launching stream, max over ranks"},
+            "e2e": {"value": round(samples / (ms_e2e / 1e3), 2), "unit": UNIT,
+                    "h2d_bytes_per_step": pts_pin.numel() * 4 + y_pin.numel() * 8, "d2h_bytes_per_step": 12},
+            "gpu_launches": launches,
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "kernel": dname, "dims": list(dargs), "achieved": None if achieved is None
+                         else round(achieved, 1), "peak": hbm, "unit": "GB/s", "frac": None if achieved is None
+                         else round(achieved / hbm, 4), "traffic": None, "peak_source": peak_src,
+                         "avg_launch_us": round(avg_s * 1e6, 2), "launches": dcount,
+                         "share_of_step": round(dms / ms_total, 4),
+                         "algorithmic_bytes_per_launch": ab},
+            "our_kernels": {"ms_total": round(ours_ms, 3), "share_of_step": round(ours_ms / ms_total, 4),
+                            "top": kern},
+        }
+        if world == 1 and not args.no_cpu:
+            sample_B = 4
+            v, cores, per = cpu_step_rate(sample_B, 1, 1)
+            out["cpu_baseline"] = {"value": round(v, 3), "unit": UNIT, "cores": cores, "kind": "port",
+                                   "sample": f"{sample_B} of the {B_PER_GPU} clouds (N={N_POINTS}), 1 warm-up + 1 timed "
+                                             f"step, {per:.1f} s/step, torch CPU threads={cores}"}
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

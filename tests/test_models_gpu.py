@@ -9,4 +9,5 @@ pytestmark = pytest.mark.gpu
 
 @pytest.mark.parametrize("case", mc.ALL, ids=lambda f: f.__name__)
 def test_module_parity_gpu(cuda_dev, case):
+    mc.strict_fp32()
     case(cuda_dev)
