@@ -9,8 +9,8 @@ so a reference state_dict (`encoder.{i}.{j}.convs.{l}.{0,1}`, `skipconv.0`, `pwc
 host infrastructure outside the path).
 
 `fused=True` (SetAbstraction / LocalAggregation) routes group -> relative position -> shared MLP -> max-pool
-through the single tcgen05 kernel of csrc/sa_fused.cu whenever the block is in eval mode (BatchNorm folded);
-the unfused path is the reference's op sequence over the same C-ABI kernels.
+through the tcgen05 kernels of csrc/sa_fused.cu whenever the block is in eval mode (BatchNorm folded) and autograd
+is off; otherwise the reference's op sequence runs over the same C-ABI kernels.
 """
 import copy
 from typing import List
@@ -35,26 +35,23 @@ def _pool_fn(reduction):
 
 
 def _fusable(grouper, convs, feature_type, reduction, training):
-    """The fused kernel covers: ball-query grouping with relative, radius-normalised dp; 'dp_fj'; one or two
-    (Conv2d 1x1 [+BN2d] [+ReLU]) layers; max reduction; BatchNorm in eval mode (folded)."""
-    if training or feature_type != "dp_fj" or reduction != "max":
-        return False
-    if not isinstance(grouper, QueryAndGroup) or not grouper.relative_xyz or grouper.return_only_idx:
-        return False
-    if len(convs) not in (1, 2):
+    """The fused kernels (csrc/sa_fused.cu) cover: ball-query grouping with relative dp; 'dp_fj'; one or two
+    (Conv2d 1x1 [+BN2d] [+ReLU]) layers; max reduction; BatchNorm in eval mode (folded); no autograd."""
+    if training or torch.is_grad_enabled() or feature_type != "dp_fj" or reduction != "max":
         return False
     for blk in convs:
         kinds = [type(m) for m in blk]
         if kinds[0] is not nn.Conv2d or any(k not in (nn.Conv2d, nn.BatchNorm2d, nn.ReLU) for k in kinds):
             return False
-    return True
+    from . import fused
+    return fused.fusable_reason(grouper, convs, getattr(grouper, "nsample", None)) is None
 
 
 def _aggregate(mod, query_p, p, f):
-    """grouper -> concat -> convs -> pool, fused into one kernel when allowed."""
+    """grouper -> concat -> convs -> pool; one fused call (tcgen05 shared MLP, no (B,C,M,K) tensors) when allowed."""
     if mod.fused and _fusable(mod.grouper, mod.convs, mod.feature_type, mod.reduction, mod.training):
         from . import fused
-        return fused.sa_fused_forward(mod.grouper, mod.convs, query_p, p, f)
+        return fused.sa_fused_forward(mod, mod.grouper, mod.convs, query_p, p, f)
     dp, fj = mod.grouper(query_p, p, f)
     return mod.pool(mod.convs(get_aggregation_feautres(query_p, dp, None, fj, "dp_fj")))
 

@@ -105,6 +105,30 @@ int apb_deform_mask_bwd_f32(const float *xyz, const float *anchor, const float *
                             const float *mask, float sigma, const float *stats, const float *grad_out,
                             float *grad_affine, float *grad_mask, int B, int N, int M, apb_stream_t stream);
 
+/* 1x1 convolution (the "shared MLP" layer: Conv1d/Conv2d kernel 1, openpoints/models/layers/conv.py:8-21, :24-103)
+ * with folded BatchNorm / bias and optional ReLU, as a bf16 tcgen05 GEMM with fp32 accumulation in TMEM:
+ *   y[b,:,p] = act(scale * (W . x[b,:,p]) + shift)
+ *   x (B,Cin,P) f32 channel-major;  w_bf16 (Cout,Kp) bf16 bits, K-major, columns >= Cin zero, Kp % 64 == 0;
+ *   scale/shift (Cout) f32 or both NULL;  y (B,Cout,P) f32.  Cout <= 512.  No native counterpart in the
+ * reference (it calls cuDNN through nn.Conv2d); tolerance vs fp32: 2e-2 relative (bf16 inputs). */
+int apb_pwconv_fwd_bf16(const float *x, const uint16_t *w_bf16, const float *scale, const float *shift, int relu,
+                        float *y, int B, int Cin, int Cout, int P, int Kp, apb_stream_t stream);
+
+/* Fused set-abstraction aggregation for BatchNorm-folded blocks: group -> relative position (/radius) ->
+ * shared MLP (1 or 2 layers) -> max over the K neighbours, without materialising any (B,C,M,K) tensor.
+ * Replaces QueryAndGroup.forward + get_aggregation_feautres('dp_fj') + convs + pool of SetAbstraction.forward
+ * (pointnext.py:164-166) and LocalAggregation.forward (pointnext.py:66-77).
+ *   xyz (B,N,3), new_xyz (B,M,3), feat (B,Cin,N) f32, idx (B,M,K) int32 (from apb_ball_query_f32 / apb_knn_f32);
+ *   first conv W1 (C1, 3+Cin) split as  w1p (3,C1) f32 = W1[:, :3]^T / radius  and  w1f_bf16 (C1,K1p) = W1[:, 3:];
+ *   s1,t1 (C1) folded BN1 (+bias); relu1;
+ *   second conv (NULL for one-layer blocks) w2_bf16 (C2,K2p), s2,t2 (C2), relu2;  K must be 32 when present;
+ *   u_ws: caller-provided workspace of B*N*C1 floats;  out (B,Cout,M) f32 with Cout = C2 (or C1). */
+int apb_sa_fused_fwd_bf16(const float *xyz, const float *new_xyz, const float *feat, const int32_t *idx,
+                          const uint16_t *w1f_bf16, const float *w1p, const float *s1, const float *t1, int relu1,
+                          const uint16_t *w2_bf16, const float *s2, const float *t2, int relu2, float *u_ws,
+                          float *out, int B, int N, int M, int K, int Cin, int C1, int K1p, int C2, int K2p,
+                          apb_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
