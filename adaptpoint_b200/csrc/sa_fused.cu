@@ -19,11 +19,11 @@
 //    TMEM, and the epilogue applies the folded BN2 and max-pools the 32 neighbour rows of a query with one
 //    CREDUX per channel -- the (B,C,M,K) activations never exist.
 //
-// tc_rows_gemm_kernel: persistent, one CTA per SM, 320 threads, warp-specialised:
+// tc_rows_gemm_kernel: persistent, one CTA per SM, 448 threads, warp-specialised:
 //    warp 0    TMA producer for the weight chunk of every pipeline stage
 //    warp 1    TMEM allocator + single-thread tcgen05.mma issuer (UMMA 128 x N x 16, bf16 -> fp32)
-//    warps 2-5 A-tile producers (128 threads): global -> registers (fp32 math) -> bf16 -> swizzled smem
-//    warps 6-9 epilogue: tcgen05.ld accumulator -> affine/ReLU -> store or K-max -> global
+//    warps 2-9 A-tile producers (2 groups of 128 threads, alternating tiles): global -> registers (fp32 math) -> bf16 -> swizzled smem
+//    warps 10-13 epilogue: tcgen05.ld accumulator -> affine/ReLU -> store or K-max -> global
 //  smem ring of STAGES x (A chunk 128x64 bf16 = 16 KB | W chunk NCPx64 bf16), full/empty mbarriers;
 //  TMEM: 512 columns, double-buffered accumulator when Cout <= 256, so the epilogue of tile t overlaps the
 //  loads + MMAs of tile t+1.
@@ -37,9 +37,10 @@ namespace {
 constexpr int BM = 128;       // rows per tile (UMMA M)
 constexpr int BK = 64;        // K elements per smem chunk = one 128-byte swizzle span of bf16
 constexpr int A_BYTES = BM * BK * 2;
-constexpr int NTHREADS = 320;
+constexpr int NGROUPS = 2;    // A-producer groups of 128 threads (alternate tiles)
 constexpr int PROD0 = 64;     // first producer thread
-constexpr int EPI0 = 192;     // first epilogue thread
+constexpr int EPI0 = PROD0 + 128 * NGROUPS;  // first epilogue thread (warp index % 4 == 2: TMEM lane quarters rotate)
+constexpr int NTHREADS = EPI0 + 128;
 constexpr int MAX_STAGES = 6;
 
 enum Loader { LOAD_CHANNEL_MAJOR = 0, LOAD_GATHER = 1 };
@@ -88,11 +89,13 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty_bar + 2);
     float *prm = reinterpret_cast<float *>(tail + 256);       // gather loader: s1,t1,wx,wy,wz [5][C1pad]
     const int c1pad = p.kchunks * BK;
-    int *meta_row = reinterpret_cast<int *>(prm + 5 * (LOADER == LOAD_GATHER ? c1pad : 0));  // [2][BM]
-    float *meta_dp = reinterpret_cast<float *>(meta_row + 2 * BM);                           // [2][3][BM]
+    int *meta_row = reinterpret_cast<int *>(prm + 5 * (LOADER == LOAD_GATHER ? c1pad : 0));  // [NGROUPS][2][BM]
+    float *meta_dp = reinterpret_cast<float *>(meta_row + NGROUPS * 2 * BM);                 // [NGROUPS][2][3][BM]
+    float *ep_ss = meta_dp + NGROUPS * 6 * BM;  // epilogue scale [512] | shift [512]
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int acc_stages = p.NCP <= 256 ? 2 : 1;
+    const uint32_t spg = p.stages / NGROUPS;  // smem stages per producer group
     const long long ntiles = (p.rows + BM - 1) / BM;
 
     if (warp == 0 && lane == 0) {
@@ -109,13 +112,20 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
     }
     if (warp == 1) tc::tmem_alloc(tmem_slot, 512);
     if (LOADER == LOAD_GATHER && tid >= PROD0 && tid < EPI0) {
-        for (int c = tid - PROD0; c < c1pad; c += 128) {
+        for (int c = tid - PROD0; c < c1pad; c += 128 * NGROUPS) {
             const bool ok = c < p.C1;
             prm[0 * c1pad + c] = ok ? p.s1[c] : 0.f;
             prm[1 * c1pad + c] = ok ? p.t1[c] : 0.f;
             prm[2 * c1pad + c] = ok ? p.Wp[0 * p.C1 + c] : 0.f;
             prm[3 * c1pad + c] = ok ? p.Wp[1 * p.C1 + c] : 0.f;
             prm[4 * c1pad + c] = ok ? p.Wp[2 * p.C1 + c] : 0.f;
+        }
+    }
+    if (tid >= EPI0) {
+        for (int c = tid - EPI0; c < 512; c += 128) {
+            const bool ok = p.scale != nullptr && c < p.Cout;
+            ep_ss[c] = ok ? p.scale[c] : 1.f;
+            ep_ss[512 + c] = ok ? p.shift[c] : 0.f;
         }
     }
     tc::tc_fence_before();
@@ -126,11 +136,13 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
     if (warp == 0) {
         // ===================== TMA producer: weight chunk of every stage =====================
         if (lane == 0) {
-            uint32_t it = 0;
-            for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            uint32_t lt = 0;
+            for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++lt) {
+                const int grp = lt % NGROUPS;
+                uint32_t it = (lt / NGROUPS) * (uint32_t)p.kchunks;  // chunk counter of this group's own stage ring
                 for (int kc = 0; kc < p.kchunks; ++kc, ++it) {
-                    const int s = it % p.stages;
-                    const uint32_t ph = (it / p.stages) & 1;
+                    const int s = grp * spg + it % spg;
+                    const uint32_t ph = (it / spg) & 1;
                     tc::mbar_wait(&empty_bar[s], ph ^ 1);
                     uint8_t *wdst = smem + (size_t)s * stage_bytes + A_BYTES;
                     tc::mbar_arrive_expect_tx(&full_bar[s], (uint32_t)p.wrows * 128);
@@ -144,16 +156,18 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
         if (lane == 0) {
             const uint32_t idesc_lo = tc::idesc_bf16_f32(BM, p.NCP <= 256 ? p.NCP : 256);
             const uint32_t idesc_hi = p.NCP > 256 ? tc::idesc_bf16_f32(BM, p.NCP - 256) : 0;
-            uint32_t it = 0, lt = 0;
+            uint32_t lt = 0;
             for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++lt) {
+                const int grp = lt % NGROUPS;
+                uint32_t it = (lt / NGROUPS) * (uint32_t)p.kchunks;
                 const int a = lt % acc_stages;
                 const uint32_t aph = (lt / acc_stages) & 1;
                 tc::mbar_wait(&tempty_bar[a], aph ^ 1);
                 tc::tc_fence_after();
                 const uint32_t tacc = tmem_base + (uint32_t)a * 256;
                 for (int kc = 0; kc < p.kchunks; ++kc, ++it) {
-                    const int s = it % p.stages;
-                    const uint32_t ph = (it / p.stages) & 1;
+                    const int s = grp * spg + it % spg;
+                    const uint32_t ph = (it / spg) & 1;
                     tc::mbar_wait(&full_bar[s], ph);
                     tc::tc_fence_after();
                     const uint32_t a_addr = tc::smem_u32(smem + (size_t)s * stage_bytes);
@@ -173,11 +187,39 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
                 tc::umma_commit(&tfull_bar[a]);      // accumulator complete -> epilogue
             }
         }
-    } else if (warp < 6) {
-        // ===================== A-tile producers (128 threads) =====================
-        const int pt = tid - PROD0;  // 0..127
-        uint32_t it = 0, lt = 0;
+    } else if (warp < 2 + 4 * NGROUPS) {
+        // ===================== A-tile producers: NGROUPS groups of 128 threads, group g fills tiles lt % NGROUPS == g
+        const int grp = (warp - 2) >> 2;
+        const int pt = (tid - PROD0) & 127;  // row of the tile (channel-major loader) / thread of the group
+        int *g_meta_row = meta_row + grp * 2 * BM;
+        float *g_meta_dp = meta_dp + grp * 6 * BM;
+        uint32_t lt = 0;
+
+        // gather loader: metadata of a tile's row `pt` (support-point row of U, dp = p[idx] - q), prefetched into
+        // registers one tile ahead so the idx -> xyz dependent loads overlap the previous tile's chunk work
+        int nx_urow = -1;
+        float nx_dx = 0.f, nx_dy = 0.f, nx_dz = 0.f;
+        auto fetch_meta = [&](long long tile) {
+            nx_urow = -1;
+            nx_dx = nx_dy = nx_dz = 0.f;
+            const long long grow = tile * BM + pt;
+            if (tile < ntiles && grow < p.rows) {
+                const long long q = grow / p.K;  // b*M + m
+                const long long b = q / p.M;
+                const int n = __ldg(p.idx + grow);
+                const float *pp = p.xyz + (b * p.N + n) * 3;
+                const float *qq = p.new_xyz + q * 3;
+                nx_dx = __ldg(pp + 0) - __ldg(qq + 0);
+                nx_dy = __ldg(pp + 1) - __ldg(qq + 1);
+                nx_dz = __ldg(pp + 2) - __ldg(qq + 2);
+                nx_urow = (int)(b * p.N + n);
+            }
+        };
+        if (LOADER == LOAD_GATHER) fetch_meta((long long)blockIdx.x + (long long)grp * gridDim.x);
+
         for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++lt) {
+            if ((int)(lt % NGROUPS) != grp) continue;
+            uint32_t it = (lt / NGROUPS) * (uint32_t)p.kchunks;  // this group's own stage ring (in-order => parity-safe)
             if (LOADER == LOAD_CHANNEL_MAJOR) {
                 // thread <-> row: lanes read 32 consecutive points of one channel (coalesced 128 B)
                 const long long grow = tile * BM + pt;
@@ -186,55 +228,57 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
                 const long long pp = valid ? grow - b * p.P : 0;
                 const float *src = p.X + (b * p.Cin) * p.P + pp;
                 for (int kc = 0; kc < p.kchunks; ++kc, ++it) {
-                    const int s = it % p.stages;
-                    const uint32_t ph = (it / p.stages) & 1;
-                    tc::mbar_wait(&empty_bar[s], ph ^ 1);
+                    const int s = grp * spg + it % spg;
+                    const uint32_t ph = (it / spg) & 1;
                     const uint32_t arow = tc::smem_u32(smem + (size_t)s * stage_bytes) + pt * 128;
+                    // all 64 loads of the chunk are issued before the first use (32 KB in flight per group)
+                    float v[64];
+                    const int cbase = kc * BK;
+                    if (valid && cbase + BK <= p.Cin) {
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        float v[8];
+                        for (int e = 0; e < 64; ++e) v[e] = __ldg(src + (size_t)(cbase + e) * p.P);
+                    } else {
 #pragma unroll
-                        for (int e = 0; e < 8; ++e) {
-                            const int c = kc * BK + j * 8 + e;
-                            v[e] = (valid && c < p.Cin) ? __ldg(src + (size_t)c * p.P) : 0.f;
-                        }
-                        tc::st_shared_v4(arow + ((j ^ (pt & 7)) << 4), tc::pack_bf16x2(v[0], v[1]),
-                                         tc::pack_bf16x2(v[2], v[3]), tc::pack_bf16x2(v[4], v[5]),
-                                         tc::pack_bf16x2(v[6], v[7]));
+                        for (int e = 0; e < 64; ++e)
+                            v[e] = (valid && cbase + e < p.Cin) ? __ldg(src + (size_t)(cbase + e) * p.P) : 0.f;
                     }
+                    tc::mbar_wait(&empty_bar[s], ph ^ 1);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        tc::st_shared_v4(arow + ((j ^ (pt & 7)) << 4), tc::pack_bf16x2(v[8 * j + 0], v[8 * j + 1]),
+                                         tc::pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
+                                         tc::pack_bf16x2(v[8 * j + 4], v[8 * j + 5]),
+                                         tc::pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
                     tc::fence_proxy_async_smem();
                     tc::mbar_arrive(&full_bar[s]);
                 }
             } else {
-                // per-tile row metadata: support-point row of U and dp = p[idx] - q
-                const int mb = lt & 1;
-                {
-                    const long long grow = tile * BM + pt;
-                    int urow = -1;
-                    float dx = 0.f, dy = 0.f, dz = 0.f;
-                    if (grow < p.rows) {
-                        const long long q = grow / p.K;           // b*M + m
-                        const long long b = q / p.M;
-                        const int n = __ldg(p.idx + grow);
-                        const float *pp = p.xyz + (b * p.N + n) * 3;
-                        const float *qq = p.new_xyz + q * 3;
-                        dx = __ldg(pp + 0) - __ldg(qq + 0);
-                        dy = __ldg(pp + 1) - __ldg(qq + 1);
-                        dz = __ldg(pp + 2) - __ldg(qq + 2);
-                        urow = (int)(b * p.N + n);
-                    }
-                    meta_row[mb * BM + pt] = urow;
-                    meta_dp[(mb * 3 + 0) * BM + pt] = dx;
-                    meta_dp[(mb * 3 + 1) * BM + pt] = dy;
-                    meta_dp[(mb * 3 + 2) * BM + pt] = dz;
-                }
-                named_bar_sync(1, 128);
+                const int mb = (lt / NGROUPS) & 1;
+                g_meta_row[mb * BM + pt] = nx_urow;
+                g_meta_dp[(mb * 3 + 0) * BM + pt] = nx_dx;
+                g_meta_dp[(mb * 3 + 1) * BM + pt] = nx_dy;
+                g_meta_dp[(mb * 3 + 2) * BM + pt] = nx_dz;
+                named_bar_sync(1 + grp, 128);
+                fetch_meta(tile + (long long)NGROUPS * gridDim.x);  // next tile of this group, consumed next round
                 // 8 lanes per row, 8 channels (32 B of U) per lane; a warp covers 4 rows per step
                 const int pw = pt >> 5, l8 = lane & 7, lr = lane >> 3;
                 for (int kc = 0; kc < p.kchunks; ++kc, ++it) {
-                    const int s = it % p.stages;
-                    const uint32_t ph = (it / p.stages) & 1;
+                    const int s = grp * spg + it % spg;
+                    const uint32_t ph = (it / spg) & 1;
                     const int c0 = kc * BK + l8 * 8;
+                    const bool cvalid = c0 < p.C1;  // C1 % 8 == 0: a lane's 8 channels are all valid or all padding
+                    // rows of U for the 8 steps, issued up front
+                    float4 u0[8], u1[8];
+                    int ur[8];
+#pragma unroll
+                    for (int step = 0; step < 8; ++step) {
+                        const int r = pw * 32 + step * 4 + lr;
+                        ur[step] = g_meta_row[mb * BM + r];
+                        const float4 *up = reinterpret_cast<const float4 *>(
+                            p.U + (size_t)(ur[step] < 0 ? 0 : ur[step]) * p.C1 + (cvalid ? c0 : 0));
+                        u0[step] = __ldg(up);
+                        u1[step] = __ldg(up + 1);
+                    }
                     float ps[8], pt1[8], wx[8], wy[8], wz[8];
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
@@ -249,33 +293,25 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
                         wy[4 * h + 0] = cy.x; wy[4 * h + 1] = cy.y; wy[4 * h + 2] = cy.z; wy[4 * h + 3] = cy.w;
                         wz[4 * h + 0] = cz.x; wz[4 * h + 1] = cz.y; wz[4 * h + 2] = cz.z; wz[4 * h + 3] = cz.w;
                     }
-                    const bool cvalid = c0 < p.C1;  // C1 % 8 == 0: a lane's 8 channels are all valid or all padding
                     tc::mbar_wait(&empty_bar[s], ph ^ 1);
                     const uint32_t abase = tc::smem_u32(smem + (size_t)s * stage_bytes);
-#pragma unroll 4
+#pragma unroll
                     for (int step = 0; step < 8; ++step) {
                         const int r = pw * 32 + step * 4 + lr;
-                        const int urow = meta_row[mb * BM + r];
-                        float v[8];
-                        if (urow >= 0 && cvalid) {
-                            const float4 *up = reinterpret_cast<const float4 *>(p.U + (size_t)urow * p.C1 + c0);
-                            const float4 u0 = __ldg(up), u1 = __ldg(up + 1);
-                            const float dx = meta_dp[(mb * 3 + 0) * BM + r];
-                            const float dy = meta_dp[(mb * 3 + 1) * BM + r];
-                            const float dz = meta_dp[(mb * 3 + 2) * BM + r];
-                            v[0] = u0.x; v[1] = u0.y; v[2] = u0.z; v[3] = u0.w;
-                            v[4] = u1.x; v[5] = u1.y; v[6] = u1.z; v[7] = u1.w;
+                        const float dx = g_meta_dp[(mb * 3 + 0) * BM + r];
+                        const float dy = g_meta_dp[(mb * 3 + 1) * BM + r];
+                        const float dz = g_meta_dp[(mb * 3 + 2) * BM + r];
+                        float v[8] = {u0[step].x, u0[step].y, u0[step].z, u0[step].w,
+                                      u1[step].x, u1[step].y, u1[step].z, u1[step].w};
+                        const bool live = ur[step] >= 0 && cvalid;
 #pragma unroll
-                            for (int e = 0; e < 8; ++e) {
-                                float y = fmaf(wx[e], dx, v[e]);
-                                y = fmaf(wy[e], dy, y);
-                                y = fmaf(wz[e], dz, y);
-                                y = fmaf(ps[e], y, pt1[e]);
-                                v[e] = p.relu1 ? fmaxf(y, 0.f) : y;
-                            }
-                        } else {
-#pragma unroll
-                            for (int e = 0; e < 8; ++e) v[e] = 0.f;
+                        for (int e = 0; e < 8; ++e) {
+                            float y = fmaf(wx[e], dx, v[e]);
+                            y = fmaf(wy[e], dy, y);
+                            y = fmaf(wz[e], dz, y);
+                            y = fmaf(ps[e], y, pt1[e]);
+                            y = p.relu1 ? fmaxf(y, 0.f) : y;
+                            v[e] = live ? y : 0.f;
                         }
                         tc::st_shared_v4(abase + r * 128 + ((l8 ^ (r & 7)) << 4), tc::pack_bf16x2(v[0], v[1]),
                                          tc::pack_bf16x2(v[2], v[3]), tc::pack_bf16x2(v[4], v[5]),
@@ -311,11 +347,8 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
                     int mine = INT_MIN;
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
-                        const int c = cb + j;
-                        float x = __uint_as_float(v[j]);
-                        if (p.scale && c < p.Cout) x = fmaf(__ldg(p.scale + c), x, __ldg(p.shift + c));
-                        const int o = tc::float_to_ordered(x);
-                        const int r = __reduce_max_sync(0xffffffffu, o);
+                        const float x = fmaf(ep_ss[cb + j], __uint_as_float(v[j]), ep_ss[512 + cb + j]);
+                        const int r = __reduce_max_sync(0xffffffffu, tc::float_to_ordered(x));
                         if (lane == j) mine = r;
                     }
                     const int c = cb + lane;
@@ -328,6 +361,7 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
             } else {
                 const long long b = valid ? grow / p.P : 0;
                 const long long pp = valid ? grow - b * p.P : 0;
+                float *ycm = p.Y + (b * p.Cout) * p.P + pp;  // EPI_STORE_CM: lanes = consecutive points (coalesced)
                 for (int cb = 0; cb < p.NCP; cb += 32) {
                     uint32_t v[32];
                     tc::tmem_ld_32x32(tacc + cb, v);
@@ -335,28 +369,35 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
                     float x[32];
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
-                        const int c = cb + j;
-                        float t = __uint_as_float(v[j]);
-                        if (p.scale && c < p.Cout) t = fmaf(__ldg(p.scale + c), t, __ldg(p.shift + c));
+                        const float t = fmaf(ep_ss[cb + j], __uint_as_float(v[j]), ep_ss[512 + cb + j]);
                         x[j] = p.relu ? fmaxf(t, 0.f) : t;
                     }
-                    if (valid) {
-                        if (EPI == EPI_STORE_CM) {
-                            float *y = p.Y + (b * p.Cout) * p.P + pp;  // lanes = consecutive points: coalesced
+                    if (EPI == EPI_STORE_CM) {
+                        if (valid) {
+                            if (cb + 32 <= p.Cout) {
 #pragma unroll
-                            for (int j = 0; j < 32; ++j)
-                                if (cb + j < p.Cout) y[(size_t)(cb + j) * p.P] = x[j];
-                        } else {
-                            float *y = p.Y + grow * p.Cout + cb;       // one 128-byte line per thread
-                            if (cb + 32 <= p.Cout && (p.Cout & 3) == 0) {
-#pragma unroll
-                                for (int j = 0; j < 32; j += 4)
-                                    *reinterpret_cast<float4 *>(y + j) = make_float4(x[j], x[j + 1], x[j + 2], x[j + 3]);
+                                for (int j = 0; j < 32; ++j) {
+                                    *ycm = x[j];
+                                    ycm += p.P;
+                                }
                             } else {
 #pragma unroll
-                                for (int j = 0; j < 32; ++j)
-                                    if (cb + j < p.Cout) y[j] = x[j];
+                                for (int j = 0; j < 32; ++j) {
+                                    if (cb + j < p.Cout) *ycm = x[j];
+                                    ycm += p.P;
+                                }
                             }
+                        }
+                    } else if (valid) {
+                        float *y = p.Y + grow * p.Cout + cb;       // one 128-byte line per thread
+                        if (cb + 32 <= p.Cout && (p.Cout & 3) == 0) {
+#pragma unroll
+                            for (int j = 0; j < 32; j += 4)
+                                *reinterpret_cast<float4 *>(y + j) = make_float4(x[j], x[j + 1], x[j + 2], x[j + 3]);
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (cb + j < p.Cout) y[j] = x[j];
                         }
                     }
                 }
@@ -475,10 +516,11 @@ int launch_tc(TcParams p, const void *Wb, int Kp, cudaStream_t st) {
     p.wrows = p.NCP <= 256 ? p.NCP : 512;
     const int stage_bytes = A_BYTES + p.wrows * 128;
     const size_t extra = 1024 /*align slack*/ + 256 /*barriers*/ +
-                         (LOADER == LOAD_GATHER ? (size_t)5 * Kp * 4 : 0) + 8 * BM * 4 /*meta*/;
+                         (LOADER == LOAD_GATHER ? (size_t)5 * Kp * 4 : 0) + (size_t)NGROUPS * 8 * BM * 4 /*meta*/ + 4096 /*epilogue scale|shift*/;
     int stages = (int)((227 * 1024 - extra) / stage_bytes);
     if (stages > MAX_STAGES) stages = MAX_STAGES;
-    if (stages < 2) return APB_E_UNSUPPORTED;
+    stages = stages / NGROUPS * NGROUPS;  // each producer group owns its own in-order ring
+    if (stages < NGROUPS) return APB_E_UNSUPPORTED;
     p.stages = stages;
     const size_t smem = (size_t)stages * stage_bytes + extra;
     CUtensorMap map;

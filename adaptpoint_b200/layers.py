@@ -16,6 +16,7 @@ import torch
 import torch.nn as nn
 
 from . import ops
+from .tcconv import TcConv1d, TcConv2d
 
 _ACTS = {
     "relu": nn.ReLU, "leakyrelu": nn.LeakyReLU, "leaky_relu": nn.LeakyReLU, "gelu": nn.GELU,
@@ -86,13 +87,13 @@ def _block(make_linear, dim, cin, cout, norm_args, act_args, order, bias):
 
 def create_convblock2d(cin, cout, norm_args=None, act_args=None, order="conv-norm-act", bias=True, **kw):
     """1x1 Conv2d (+norm)(+act); conv bias is dropped when a norm follows (conv.py:24-60)."""
-    return _block(lambda i, o, b: nn.Conv2d(i, o, (1, 1), bias=b, **kw), "2d", cin, cout, norm_args, act_args,
+    return _block(lambda i, o, b: TcConv2d(i, o, (1, 1), bias=b, **kw), "2d", cin, cout, norm_args, act_args,
                   order, bias)
 
 
 def create_convblock1d(cin, cout, norm_args=None, act_args=None, order="conv-norm-act", bias=True, **kw):
     """1x1 Conv1d (+norm)(+act) (conv.py:63-103)."""
-    return _block(lambda i, o, b: nn.Conv1d(i, o, 1, bias=b, **kw), "1d", cin, cout, norm_args, act_args, order,
+    return _block(lambda i, o, b: TcConv1d(i, o, 1, bias=b, **kw), "1d", cin, cout, norm_args, act_args, order,
                   bias)
 
 

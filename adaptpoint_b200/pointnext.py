@@ -40,8 +40,7 @@ def _fusable(grouper, convs, feature_type, reduction, training):
     if training or torch.is_grad_enabled() or feature_type != "dp_fj" or reduction != "max":
         return False
     for blk in convs:
-        kinds = [type(m) for m in blk]
-        if kinds[0] is not nn.Conv2d or any(k not in (nn.Conv2d, nn.BatchNorm2d, nn.ReLU) for k in kinds):
+        if not isinstance(blk[0], nn.Conv2d) or any(not isinstance(m, (nn.Conv2d, nn.BatchNorm2d, nn.ReLU)) for m in blk):
             return False
     from . import fused
     return fused.fusable_reason(grouper, convs, getattr(grouper, "nsample", None)) is None

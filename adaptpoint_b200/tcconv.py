@@ -1,0 +1,120 @@
+"""1x1 convolutions (the "shared MLP" layers) on the tensor cores, forward AND backward, for training.
+
+nn.Conv1d / nn.Conv2d with kernel 1 is what every conv of the path is in the reference
+(openpoints/models/layers/conv.py:8-21: Conv1d/Conv2d wrappers; create_convblock1d/2d :24-103); torch runs them
+through cuDNN.  `TcConv1d` / `TcConv2d` keep the parameters, names and state_dict of nn.Conv{1,2}d and, when the
+backend switch is "tc", run
+    y  = W x (+b)            apb_pwconv_fwd_bf16   (bf16 operands, fp32 accumulate, tcgen05)
+    gx = W^T gy              apb_pwconv_fwd_bf16 on the transposed weights
+    gW = gy x^T              apb_pwconv_wgrad_tf32 (TF32, both operands TMA-fed)
+Numerics: 2e-2 relative (BASELINE.json north_star, "bf16 MLP path").  With the switch at "torch" (default) they
+are plain nn.Conv{1,2}d (strict fp32 parity tests use that).
+"""
+import contextlib
+
+import torch
+import torch.nn as nn
+from torch.autograd import Function
+
+from . import _cabi
+from .fused import pack_bf16
+
+_BACKEND = "torch"
+_MAX_N = 512  # accumulator columns of one kernel call
+
+
+def set_conv_backend(name):
+    """'torch' (cuDNN, fp32) or 'tc' (libapb200 tensor-core kernels)."""
+    global _BACKEND
+    if name not in ("torch", "tc"):
+        raise ValueError(name)
+    _BACKEND = name
+
+
+def get_conv_backend():
+    return _BACKEND
+
+
+@contextlib.contextmanager
+def conv_backend(name):
+    prev = _BACKEND
+    set_conv_backend(name)
+    try:
+        yield
+    finally:
+        set_conv_backend(prev)
+
+
+def _gemm_rows(x, w2d, bias, B, cin, cout, P):
+    """y (B,cout,P) = w2d (cout,cin) . x (B,cin,P) (+bias) through apb_pwconv_fwd_bf16, splitting cout > 512."""
+    outs = []
+    for c0 in range(0, cout, _MAX_N):
+        c1 = min(cout, c0 + _MAX_N)
+        wb, kp = pack_bf16(w2d[c0:c1])
+        y = torch.empty((B, c1 - c0, P), dtype=torch.float32, device=x.device)
+        if bias is not None:
+            scale = torch.ones(c1 - c0, dtype=torch.float32, device=x.device)
+            shift = bias[c0:c1].contiguous().float()
+        else:
+            scale = shift = None
+        _cabi.call("apb_pwconv_fwd_bf16", [x, wb, scale, shift, 0, y, B, cin, c1 - c0, P, kp], x.device)
+        outs.append(y)
+    return outs[0] if len(outs) == 1 else torch.cat(outs, dim=1)
+
+
+class PointwiseConvFn(Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        shp = x.shape
+        B, cin = shp[0], shp[1]
+        P = 1
+        for d in shp[2:]:
+            P *= d
+        cout = weight.shape[0]
+        xs = x.detach().contiguous().float()
+        w2d = weight.detach().reshape(cout, cin).float()
+        y = _gemm_rows(xs, w2d, None if bias is None else bias.detach(), B, cin, cout, P)
+        ctx.save_for_backward(xs, weight)
+        ctx.has_bias = bias is not None
+        ctx.dims = (B, cin, cout, P, tuple(shp))
+        return y.view((B, cout) + tuple(shp[2:]))
+
+    @staticmethod
+    def backward(ctx, gy):
+        xs, weight = ctx.saved_tensors
+        B, cin, cout, P, shp = ctx.dims
+        g = gy.detach().contiguous().float().view(B, cout, P)
+        gx = gw = gb = None
+        if ctx.needs_input_grad[0]:
+            wt = weight.detach().reshape(cout, cin).float().t().contiguous()
+            gx = _gemm_rows(g, wt, None, B, cout, cin, P).view(shp)
+        if ctx.needs_input_grad[1]:
+            if P % 4 == 0:
+                gw = torch.zeros((cout, cin), dtype=torch.float32, device=g.device)
+                _cabi.call("apb_pwconv_wgrad_tf32", [g, xs.view(B, cin, P), gw, B, cin, cout, P], g.device)
+            else:  # TMA needs 16-byte aligned rows; odd point counts do not occur on the PointNeXt path
+                gw = torch.einsum("bop,bip->oi", g, xs.view(B, cin, P))
+            gw = gw.view(weight.shape)
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            gb = g.sum(dim=(0, 2))
+        return gx, gw, gb
+
+
+def _use_tc(mod, x):
+    return (_BACKEND == "tc" and x.is_cuda and x.dtype == torch.float32 and mod.groups == 1
+            and all(k == 1 for k in mod.kernel_size) and all(s == 1 for s in mod.stride)
+            and all(p == 0 for p in mod.padding))
+
+
+class TcConv1d(nn.Conv1d):
+    def forward(self, x):
+        if _use_tc(self, x):
+            return PointwiseConvFn.apply(x, self.weight, self.bias)
+        return super().forward(x)
+
+
+class TcConv2d(nn.Conv2d):
+    def forward(self, x):
+        if _use_tc(self, x):
+            return PointwiseConvFn.apply(x, self.weight, self.bias)
+        return super().forward(x)

@@ -21,7 +21,7 @@ import torch
 import torch.distributed as dist
 import torch.nn as nn
 
-from . import ops
+from . import ops, tcconv
 from .imitator import AdaptPoint_Augmentor, PointDiscriminator1, PointWOLF_classversion
 from .models import SmoothCrossEntropy, build_model
 
@@ -72,9 +72,12 @@ class AdaptPointTrainer:
     """Holds classifier / imitator / discriminator + their optimizers; `step(batch)` = one train_gan iteration
     followed by one train_one_epoch iteration on the generated batch."""
 
-    def __init__(self, cfg=None, device="cuda", fused_eval=False, seed=0):
+    def __init__(self, cfg=None, device="cuda", fused_eval=False, seed=0, conv_backend="tc"):
+        """conv_backend: 'tc' = every 1x1 convolution (fwd, dgrad, wgrad) on the tcgen05 kernels of libapb200
+        (bf16/TF32 operands, fp32 accumulation); 'torch' = cuDNN fp32 (strict-parity runs)."""
         self.cfg = copy.deepcopy(ADAPTPOINT_CFG if cfg is None else cfg)
         self.device = torch.device(device)
+        self.conv_backend = conv_backend if self.device.type == "cuda" else "torch"
         torch.manual_seed(seed)
         self.classifier = build_model(self.cfg["model"], fused=fused_eval).to(self.device)
         self.generator = AdaptPoint_Augmentor(**self.cfg["adaptmodel_gan"]).to(self.device)
@@ -162,6 +165,7 @@ class AdaptPointTrainer:
 
     def step(self, points, label):
         """One full AdaptPoint step on a loader-shaped batch.  Returns (cls_loss, g_loss, d_loss) tensors."""
-        fake, g_loss, d_loss = self.gan_iteration(points, label)
-        _, loss = self.classifier_iteration(fake, label)
+        with tcconv.conv_backend(self.conv_backend):
+            fake, g_loss, d_loss = self.gan_iteration(points, label)
+            _, loss = self.classifier_iteration(fake, label)
         return loss, g_loss, d_loss

@@ -114,6 +114,13 @@ int apb_deform_mask_bwd_f32(const float *xyz, const float *anchor, const float *
 int apb_pwconv_fwd_bf16(const float *x, const uint16_t *w_bf16, const float *scale, const float *shift, int relu,
                         float *y, int B, int Cin, int Cout, int P, int Kp, apb_stream_t stream);
 
+/* Weight gradient of the 1x1 convolution above (TF32 tcgen05, both operands TMA-fed):
+ *   grad_w[co,ci] += sum_{b,p} grad_y[b,co,p] * x[b,ci,p];  grad_w (Cout,Cin) f32 pre-zeroed by the caller.
+ *   grad_y (B,Cout,P), x (B,Cin,P) f32 channel-major, P % 4 == 0 (else APB_E_UNSUPPORTED).
+ * The data gradient is apb_pwconv_fwd_bf16 on grad_y with the transposed weights. */
+int apb_pwconv_wgrad_tf32(const float *grad_y, const float *x, float *grad_w, int B, int Cin, int Cout, int P,
+                          apb_stream_t stream);
+
 /* Fused set-abstraction aggregation for BatchNorm-folded blocks: group -> relative position (/radius) ->
  * shared MLP (1 or 2 layers) -> max over the K neighbours, without materialising any (B,C,M,K) tensor.
  * Replaces QueryAndGroup.forward + get_aggregation_feautres('dp_fj') + convs + pool of SetAbstraction.forward

@@ -1,0 +1,47 @@
+"""Small single-op programs for `ncu --set full` captures:  python scripts/ncu_targets.py <target>
+targets: sa2 (two-layer fused SA, PointNeXt-S stage 1, B=32), pw (1x1 conv 512->512), fps, group, group_grad"""
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from adaptpoint_b200 import _cabi, fused, ops  # noqa: E402
+from adaptpoint_b200.layers import create_convblock1d  # noqa: E402
+from adaptpoint_b200.pointnext import LocalAggregation  # noqa: E402
+from adaptpoint_b200.synth import make_clouds  # noqa: E402
+
+dev = torch.device("cuda:0")
+tgt = sys.argv[1] if len(sys.argv) > 1 else "sa2"
+if tgt == "sa2":
+    B, N, M, cin, ch, r = 32, 2048, 1024, 32, [32, 64], 0.15
+    la = LocalAggregation([cin] + ch, norm_args={"norm": "bn"}, act_args={"act": "relu"},
+                          group_args={"NAME": "ballquery", "radius": r, "nsample": 32, "normalize_dp": True},
+                          last_act=False).to(dev).eval()
+    xyz = make_clouds(B, N, "shell", 0).to(dev)
+    f = torch.randn(B, cin, N, device=dev)
+    ix = ops.furthest_point_sample(xyz, M).long()
+    q = torch.gather(xyz, 1, ix.unsqueeze(-1).expand(-1, -1, 3)).contiguous()
+    for _ in range(3):
+        fused.sa_fused_forward(la, la.grouper, la.convs, q, xyz, f)
+elif tgt == "pw":
+    blk = create_convblock1d(512, 512, norm_args={"norm": "bn1d"}, act_args={"act": "relu"}).to(dev).eval()
+    x = torch.randn(8, 512, 65536, device=dev)
+    for _ in range(3):
+        fused.pwconv_forward(blk, x)
+elif tgt in ("fps", "group", "group_grad"):
+    B, N, M, K, C = 32, 16384, 4096, 32, 32
+    xyz = make_clouds(B, N, "shell", 0).to(dev)
+    for _ in range(2):
+        idx = ops.furthest_point_sample(xyz, M)
+    if tgt != "fps":
+        q = torch.gather(xyz, 1, idx.long().unsqueeze(-1).expand(-1, -1, 3)).contiguous()
+        nbr = ops.ball_query(0.1, K, xyz, q)
+        feat = torch.randn(B, C, N, device=dev, requires_grad=True)
+        for _ in range(2):
+            g = ops.grouping_operation(feat, nbr)
+            if tgt == "group_grad":
+                g.backward(torch.ones_like(g))
+torch.cuda.synchronize()
+print("done", tgt)

@@ -25,7 +25,8 @@ def _randomise_bn(mod, gen):
 
 @pytest.mark.parametrize("B,cin,cout,P,relu", [(2, 4, 32, 1024, True), (3, 35, 64, 777, False),
                                                (2, 131, 128, 300, True), (1, 259, 256, 129, True),
-                                               (2, 64, 512, 260, False), (1, 515, 40, 64, True)])
+                                               (2, 64, 512, 260, False), (1, 515, 40, 64, True),
+                                               (8, 259, 256, 8192, True), (4, 512, 512, 20000, False)])
 def test_pwconv_matches_fp32(cuda_dev, B, cin, cout, P, relu):
     from adaptpoint_b200 import fused
     from adaptpoint_b200.layers import create_convblock1d
@@ -78,6 +79,8 @@ def _sa_case(cuda_dev, B, N, M, cin, channels, radius, seed, normalize_dp=True):
     (2, 512, 256, 64, [64, 128], 0.225),     # stage 2
     (3, 256, 128, 128, [128, 256], 0.3375),  # stage 3
     (2, 128, 64, 256, [256, 512], 0.50625),  # stage 4 (Cout 512: single-buffered accumulator)
+    (32, 128, 64, 256, [256, 512], 0.50625), # same, several tiles per CTA with a 1-deep ring per producer group
+    (32, 1024, 512, 32, [32, 64], 0.15),     # full-batch stage 1: 28 tiles per CTA
     (1, 1000, 250, 16, [24, 40], 0.2),       # ragged channel counts
     (1, 333, 333, 8, [16, 16], 0.3),         # B*M*K not a multiple of 128
 ])

@@ -1,0 +1,90 @@
+"""Training-path 1x1 convolutions on the tensor cores (tcconv.PointwiseConvFn: apb_pwconv_fwd_bf16 for y and gx,
+apb_pwconv_wgrad_tf32 for gW) against torch's fp32 convolution + autograd; tolerance 2e-2 relative (bf16/TF32
+operands, fp32 accumulation)."""
+import pytest
+import torch
+import torch.nn as nn
+
+pytestmark = pytest.mark.gpu
+TOL = 2e-2
+
+
+def _rel(got, want):
+    return ((got - want).abs().max() / want.abs().max().clamp_min(1e-6)).item()
+
+
+@pytest.mark.parametrize("B,cin,cout,shape,bias", [
+    (4, 35, 32, (512, 32), False),     # SA stage-1 conv1 on the grouped tensor
+    (4, 32, 64, (512, 32), False),     # conv2
+    (2, 259, 256, (64, 32), False),    # stage 4
+    (2, 256, 512, (64, 32), True),
+    (3, 4, 32, (1024,), True),         # head Conv1d
+    (2, 128, 1024, (2048,), True),     # discriminator: Cout > 512 is split
+    (2, 515, 64, (96,), False),        # Cin > 512: data gradient is split
+    (2, 64, 3, (1000,), False),        # tiny Cout
+    (2, 16, 24, (333,), True),         # P % 4 != 0: weight gradient falls back to einsum
+])
+def test_pointwise_conv_fwd_bwd(cuda_dev, B, cin, cout, shape, bias):
+    from adaptpoint_b200 import tcconv
+    gen = torch.Generator().manual_seed(cin + cout)
+    Conv = tcconv.TcConv2d if len(shape) == 2 else tcconv.TcConv1d
+    conv = Conv(cin, cout, 1, bias=bias).to(cuda_dev)
+    x = torch.randn((B, cin) + shape, generator=gen).to(cuda_dev).requires_grad_(True)
+    gy = torch.randn((B, cout) + shape, generator=gen).to(cuda_dev)
+    want = conv(x)
+    want.backward(gy)
+    ref = [x.grad.clone(), conv.weight.grad.clone(), None if not bias else conv.bias.grad.clone()]
+    x.grad = None
+    conv.zero_grad()
+    with tcconv.conv_backend("tc"):
+        got = conv(x)
+        got.backward(gy)
+    assert got.shape == want.shape
+    assert _rel(got, want) < TOL
+    assert _rel(x.grad, ref[0]) < TOL
+    assert _rel(conv.weight.grad, ref[1]) < TOL
+    if bias:
+        assert _rel(conv.bias.grad, ref[2]) < 1e-4
+
+
+def test_wgrad_large_k_split(cuda_dev):
+    """Many K chunks per CTA and two Cin tiles."""
+    from adaptpoint_b200 import _cabi
+    gen = torch.Generator().manual_seed(0)
+    B, cin, cout, P = 8, 300, 200, 4096
+    x = torch.randn(B, cin, P, generator=gen).to(cuda_dev)
+    gy = torch.randn(B, cout, P, generator=gen).to(cuda_dev)
+    gw = torch.zeros(cout, cin, device=cuda_dev)
+    _cabi.call("apb_pwconv_wgrad_tf32", [gy, x, gw, B, cin, cout, P], cuda_dev)
+    want = torch.einsum("bop,bip->oi", gy.double(), x.double()).float()
+    assert _rel(gw, want) < 5e-3
+
+
+def test_model_step_tc_vs_fp32(cuda_dev):
+    """PointNeXt-S training-mode loss and a few gradients: tensor-core convs vs cuDNN fp32, same parameters."""
+    from adaptpoint_b200 import tcconv
+    from adaptpoint_b200.models import build_model
+    from adaptpoint_b200.synth import make_clouds
+    torch.manual_seed(0)
+    model = build_model("pointnext-s").to(cuda_dev).train()
+    xyz = make_clouds(8, 1024, "shell", 3).to(cuda_dev)
+    x = torch.cat([xyz, xyz[:, :, 1:2] - xyz[:, :, 1:2].amin(1, keepdim=True)], -1).transpose(1, 2).contiguous()
+    y = torch.arange(8, device=cuda_dev) % 15
+    outs = {}
+    for backend in ("torch", "tc"):
+        model.zero_grad()
+        torch.manual_seed(7)                       # same Dropout masks in both runs
+        with tcconv.conv_backend(backend):
+            logits, loss = model.get_logits_loss({"pos": xyz, "x": x}, y)
+            loss.backward()
+        grads = {n: p.grad.clone() for n, p in model.named_parameters() if p.grad is not None}
+        outs[backend] = (logits.detach().clone(), loss.item(), grads)
+    assert abs(outs["tc"][1] - outs["torch"][1]) < 2e-2 * max(1.0, abs(outs["torch"][1]))
+    assert _rel(outs["tc"][0], outs["torch"][0]) < 5e-2
+    # gradients pass through six bf16 stages + training-mode BatchNorm: compare direction, not digits
+    for n, g in outs["torch"][2].items():
+        gt = outs["tc"][2][n]
+        if g.numel() < 64 or g.norm() < 1e-6:
+            continue
+        cos = torch.nn.functional.cosine_similarity(g.flatten(), gt.flatten(), dim=0).item()
+        assert cos > 0.98, (n, cos)
