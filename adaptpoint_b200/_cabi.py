@@ -30,6 +30,7 @@ _SIGNATURES = {
     "apb_deform_mask_fwd_f32": [_p, _p, _p, _p, _p, _f, _p, _p, _i, _i, _i, _p],
     "apb_deform_mask_bwd_f32": [_p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _i, _i, _i, _p],
     "apb_pwconv_fwd_bf16": [_p, _p, _p, _p, _i, _p, _i, _i, _i, _i, _i, _p],
+    "apb_pwconv_fwd_tf32": [_p, _p, _p, _p, _i, _p, _i, _i, _i, _i, _i, _p],
     "apb_pwconv_wgrad_tf32": [_p, _p, _p, _i, _i, _i, _i, _p],
     "apb_sa_fused_fwd_bf16": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _i, _p, _p,
                               _i, _i, _i, _i, _i, _i, _i, _i, _i, _p],

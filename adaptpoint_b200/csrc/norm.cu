@@ -1,0 +1,207 @@
+// BatchNorm (training mode, batch statistics) (+ReLU) and BatchNorm + max-pool over the K neighbours, for the
+// channel-major (B, C, P) activations of the shared MLP.  HBM-bound streaming kernels.
+//
+// They replace, behind the same nn.BatchNorm{1,2}d parameters (openpoints/models/layers/norm.py:57-71 'bn1d'/'bn2d',
+// conv.py:24-103 conv-norm-act blocks) and the max reduction of SetAbstraction / LocalAggregation
+// (pointnext.py:134, :74-77), what torch runs as cudnn/native batch_norm (+threshold) (+max over the last dim):
+//   forward  BN(+ReLU):  one read pass for the statistics, one read+write pass to apply      (torch: same + ReLU pass)
+//   backward BN(+ReLU):  one read pass (sum dy, sum dy*xhat), one read+write pass            (torch native: ~5x slower)
+//   forward  BN -> max_K: ONE read pass: per-channel sum / sum of squares AND per-(b,c,m) max, min, arg over K;
+//                         BN is monotone per channel, so max_k BN(y) = BN(max_k y) if gamma >= 0 else BN(min_k y):
+//                         the normalised (B,C,M,K) tensor is never written;
+//   backward BN -> max_K: dy = gsel * [k == arg] + a[c] + b[c] * y   (the batch-statistics terms of the BatchNorm
+//                         backward are affine in y), one read + one write pass.
+// Statistics are accumulated per CTA in fp32 over <= 4096 elements and across CTAs in fp64 (atomicAdd double).
+#include "apb_common.cuh"
+
+namespace {
+
+constexpr int NT = 256;
+constexpr int CHUNK = 4096;  // elements of one (b, c) row handled by a CTA
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// block-wide sum of two values; result valid in thread 0
+__device__ __forceinline__ void block_sum2(float &a, float &b) {
+    __shared__ float red[2][NT / 32];
+    a = warp_sum(a);
+    b = warp_sum(b);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) { red[0][warp] = a; red[1][warp] = b; }
+    __syncthreads();
+    if (warp == 0) {
+        a = lane < NT / 32 ? red[0][lane] : 0.f;
+        b = lane < NT / 32 ? red[1][lane] : 0.f;
+        a = warp_sum(a);
+        b = warp_sum(b);
+    }
+}
+
+// stats[c] += (sum x, sum x^2) over this CTA's chunk of row (b, c)
+__global__ void __launch_bounds__(NT) bn_stats_kernel(const float *__restrict__ x, double *__restrict__ stats, int C,
+                                                      long long P) {
+    const int c = blockIdx.y, b = blockIdx.z;
+    const float *row = x + ((size_t)b * C + c) * P;
+    const long long p0 = (long long)blockIdx.x * CHUNK;
+    const long long p1 = min(P, p0 + CHUNK);
+    float s = 0.f, q = 0.f;
+    if ((P & 3) == 0 && (reinterpret_cast<uintptr_t>(row) & 15) == 0) {
+        for (long long p = p0 + threadIdx.x * 4; p < p1; p += NT * 4) {
+            const float4 v = apb_ld_nc_f4(row + p);
+            s += (v.x + v.y) + (v.z + v.w);
+            q += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
+        }
+    } else {
+        for (long long p = p0 + threadIdx.x; p < p1; p += NT) {
+            const float v = __ldg(row + p);
+            s += v;
+            q += v * v;
+        }
+    }
+    block_sum2(s, q);
+    if (threadIdx.x == 0) {
+        atomicAdd(stats + 2 * c, (double)s);
+        atomicAdd(stats + 2 * c + 1, (double)q);
+    }
+}
+
+struct BnApplyParams {
+    const float *x;
+    float *y;
+    const double *stats;
+    const float *gamma, *beta;
+    float eps;
+    double inv_count;  // 1 / (elements per channel over all ranks)
+    double unbias;     // n / (n - 1)
+    int relu;
+    float *save_mean, *save_rstd, *running_mean, *running_var;  // running_* may be null
+    float momentum;
+    int C;
+    long long P;
+};
+
+__global__ void __launch_bounds__(NT) bn_apply_kernel(const BnApplyParams p) {
+    const int c = blockIdx.y, b = blockIdx.z;
+    const double mean_d = p.stats[2 * c] * p.inv_count;
+    double var_d = p.stats[2 * c + 1] * p.inv_count - mean_d * mean_d;
+    if (var_d < 0.0) var_d = 0.0;
+    const float mean = (float)mean_d;
+    const float rstd = (float)(1.0 / sqrt(var_d + (double)p.eps));
+    const float scale = p.gamma[c] * rstd;
+    const float shift = p.beta[c] - mean * scale;
+    if (blockIdx.x == 0 && b == 0 && threadIdx.x == 0) {
+        p.save_mean[c] = mean;
+        p.save_rstd[c] = rstd;
+        if (p.running_mean) {
+            p.running_mean[c] = (1.f - p.momentum) * p.running_mean[c] + p.momentum * mean;
+            p.running_var[c] = (1.f - p.momentum) * p.running_var[c] + p.momentum * (float)(var_d * p.unbias);
+        }
+    }
+    const float *row = p.x + ((size_t)b * p.C + c) * p.P;
+    float *out = p.y + ((size_t)b * p.C + c) * p.P;
+    const long long p0 = (long long)blockIdx.x * CHUNK;
+    const long long p1 = min(p.P, p0 + CHUNK);
+    if ((p.P & 3) == 0 && ((reinterpret_cast<uintptr_t>(row) | reinterpret_cast<uintptr_t>(out)) & 15) == 0) {
+        for (long long i = p0 + threadIdx.x * 4; i < p1; i += NT * 4) {
+            float4 v = apb_ld_nc_f4(row + i);
+            v.x = fmaf(v.x, scale, shift); v.y = fmaf(v.y, scale, shift);
+            v.z = fmaf(v.z, scale, shift); v.w = fmaf(v.w, scale, shift);
+            if (p.relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+            *reinterpret_cast<float4 *>(out + i) = v;
+        }
+    } else {
+        for (long long i = p0 + threadIdx.x; i < p1; i += NT) {
+            float v = fmaf(__ldg(row + i), scale, shift);
+            out[i] = p.relu ? fmaxf(v, 0.f) : v;
+        }
+    }
+}
+
+// stats2[c] += (sum dy', sum dy' * xhat), dy' = dy * [y > 0] when `y` (the ReLU output) is given
+__global__ void __launch_bounds__(NT) bn_bwd_reduce_kernel(const float *__restrict__ x, const float *__restrict__ dy,
+                                                           const float *__restrict__ y,
+                                                           const float *__restrict__ save_mean,
+                                                           const float *__restrict__ save_rstd,
+                                                           double *__restrict__ stats2, int C, long long P) {
+    const int c = blockIdx.y, b = blockIdx.z;
+    const size_t off = ((size_t)b * C + c) * P;
+    const float mean = save_mean[c], rstd = save_rstd[c];
+    const long long p0 = (long long)blockIdx.x * CHUNK;
+    const long long p1 = min(P, p0 + CHUNK);
+    float s = 0.f, q = 0.f;
+    const bool vec = (P & 3) == 0 && (((reinterpret_cast<uintptr_t>(x + off) | reinterpret_cast<uintptr_t>(dy + off) |
+                                        (y ? reinterpret_cast<uintptr_t>(y + off) : 0)) & 15) == 0);
+    if (vec) {
+        for (long long i = p0 + threadIdx.x * 4; i < p1; i += NT * 4) {
+            const float4 xv = apb_ld_nc_f4(x + off + i);
+            float4 g = apb_ld_nc_f4(dy + off + i);
+            if (y) {
+                const float4 yv = apb_ld_nc_f4(y + off + i);
+                g.x = yv.x > 0.f ? g.x : 0.f; g.y = yv.y > 0.f ? g.y : 0.f;
+                g.z = yv.z > 0.f ? g.z : 0.f; g.w = yv.w > 0.f ? g.w : 0.f;
+            }
+            s += (g.x + g.y) + (g.z + g.w);
+            q += (g.x * (xv.x - mean) + g.y * (xv.y - mean)) + (g.z * (xv.z - mean) + g.w * (xv.w - mean));
+        }
+    } else {
+        for (long long i = p0 + threadIdx.x; i < p1; i += NT) {
+            float g = __ldg(dy + off + i);
+            if (y && !(__ldg(y + off + i) > 0.f)) g = 0.f;
+            s += g;
+            q += g * (__ldg(x + off + i) - mean);
+        }
+    }
+    q *= rstd;
+    block_sum2(s, q);
+    if (threadIdx.x == 0) {
+        atomicAdd(stats2 + 2 * c, (double)s);
+        atomicAdd(stats2 + 2 * c + 1, (double)q);
+    }
+}
+
+// dx = gamma * rstd * (dy' - sum(dy')/n - xhat * sum(dy' xhat)/n)
+__global__ void __launch_bounds__(NT) bn_bwd_apply_kernel(const float *__restrict__ x, const float *__restrict__ dy,
+                                                          const float *__restrict__ y,
+                                                          const float *__restrict__ save_mean,
+                                                          const float *__restrict__ save_rstd,
+                                                          const float *__restrict__ gamma,
+                                                          const double *__restrict__ stats2, double inv_count,
+                                                          float *__restrict__ dx, int C, long long P) {
+    const int c = blockIdx.y, b = blockIdx.z;
+    const size_t off = ((size_t)b * C + c) * P;
+    const float mean = save_mean[c], rstd = save_rstd[c];
+    const float k0 = gamma[c] * rstd;
+    const float m1 = (float)(stats2[2 * c] * inv_count);            // mean of dy'
+    const float m2 = (float)(stats2[2 * c + 1] * inv_count) * rstd; // mean of dy' xhat, times rstd
+    // dx = k0 * (g - m1 - (x - mean) * m2)
+    const long long p0 = (long long)blockIdx.x * CHUNK;
+    const long long p1 = min(P, p0 + CHUNK);
+    const bool vec = (P & 3) == 0 && (((reinterpret_cast<uintptr_t>(x + off) | reinterpret_cast<uintptr_t>(dy + off) |
+                                        reinterpret_cast<uintptr_t>(dx + off) |
+                                        (y ? reinterpret_cast<uintptr_t>(y + off) : 0)) & 15) == 0);
+    if (vec) {
+        for (long long i = p0 + threadIdx.x * 4; i < p1; i += NT * 4) {
+            const float4 xv = apb_ld_nc_f4(x + off + i);
+            float4 g = apb_ld_nc_f4(dy + off + i);
+            if (y) {
+                const float4 yv = apb_ld_nc_f4(y + off + i);
+                g.x = yv.x > 0.f ? g.x : 0.f; g.y = yv.y > 0.f ? g.y : 0.f;
+                g.z = yv.z > 0.f ? g.z : 0.f; g.w = yv.w > 0.f ? g.w : 0.f;
+            }
+            float4 o;
+            o.x = k0 * (g.x - m1 - (xv.x - mean) * m2); o.y = k0 * (g.y - m1 - (xv.y - mean) * m2);
+            o.z = k0 * (g.z - m1 - (xv.z - mean) * m2); o.w = k0 * (g.w - m1 - (xv.w - mean) * m2);
+            *reinterpret_cast<float4 *>(dx + off + i) = o;
+        }
+    } else {
+        for (long long i = p0 + threadIdx.x; i < p1; i += NT) {
+            float g = __ldg(dy + off + i);
+            if (y && !(__ldg(y + off + i) > 0.f)) g = 0.f;
+            dx[off + i] = k0 * (g - m1 - (__ldg(x + off + i) - mean) * m2);
+        }
+    }
+}

@@ -35,8 +35,7 @@
 namespace {
 
 constexpr int BM = 128;       // rows per tile (UMMA M)
-constexpr int BK = 64;        // K elements per smem chunk = one 128-byte swizzle span of bf16
-constexpr int A_BYTES = BM * BK * 2;
+constexpr int A_BYTES = BM * 128;  // A chunk: 128 rows x one 128-byte swizzle span (64 bf16 or 32 tf32)
 constexpr int NGROUPS = 2;    // A-producer groups of 128 threads (alternate tiles)
 constexpr int PROD0 = 64;     // first producer thread
 constexpr int EPI0 = PROD0 + 128 * NGROUPS;  // first epilogue thread (warp index % 4 == 2: TMEM lane quarters rotate)
@@ -74,9 +73,13 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
-template <int LOADER, int EPI>
+// TF32 = false: bf16 operands (64 per 128-byte chunk), kind::f16.  TF32 = true: fp32 operands rounded to tf32 (32 per
+// chunk), kind::tf32 -- the training path, where bf16 operand rounding measurably perturbs the gradients of this
+// max-pool / ReLU-routed network (tests/test_tcconv_gpu.py).
+template <int LOADER, int EPI, bool TF32>
 __global__ void __launch_bounds__(NTHREADS, 1)
 tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) {
+    constexpr int BKE = TF32 ? 32 : 64;  // K elements per 128-byte chunk
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     // 1024-byte alignment is required by the 128B swizzle; dynamic smem base is only guaranteed 16 B
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -88,7 +91,7 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
     uint64_t *tempty_bar = tfull_bar + 2;                     // [2]
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty_bar + 2);
     float *prm = reinterpret_cast<float *>(tail + 256);       // gather loader: s1,t1,wx,wy,wz [5][C1pad]
-    const int c1pad = p.kchunks * BK;
+    const int c1pad = p.kchunks * BKE;
     int *meta_row = reinterpret_cast<int *>(prm + 5 * (LOADER == LOAD_GATHER ? c1pad : 0));  // [NGROUPS][2][BM]
     float *meta_dp = reinterpret_cast<float *>(meta_row + NGROUPS * 2 * BM);                 // [NGROUPS][2][3][BM]
     float *ep_ss = meta_dp + NGROUPS * 6 * BM;  // epilogue scale [512] | shift [512]
@@ -146,16 +149,17 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
                     tc::mbar_wait(&empty_bar[s], ph ^ 1);
                     uint8_t *wdst = smem + (size_t)s * stage_bytes + A_BYTES;
                     tc::mbar_arrive_expect_tx(&full_bar[s], (uint32_t)p.wrows * 128);
-                    tc::tma_load_2d(wdst, &wmap, kc * BK, 0, &full_bar[s]);
-                    if (p.wrows > 256) tc::tma_load_2d(wdst + 256 * 128, &wmap, kc * BK, 256, &full_bar[s]);
+                    tc::tma_load_2d(wdst, &wmap, kc * BKE, 0, &full_bar[s]);
+                    if (p.wrows > 256) tc::tma_load_2d(wdst + 256 * 128, &wmap, kc * BKE, 256, &full_bar[s]);
                 }
             }
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
         if (lane == 0) {
-            const uint32_t idesc_lo = tc::idesc_bf16_f32(BM, p.NCP <= 256 ? p.NCP : 256);
-            const uint32_t idesc_hi = p.NCP > 256 ? tc::idesc_bf16_f32(BM, p.NCP - 256) : 0;
+            const int n_lo = p.NCP <= 256 ? p.NCP : 256, n_hi = p.NCP > 256 ? p.NCP - 256 : 16;
+            const uint32_t idesc_lo = TF32 ? tc::idesc_tf32_f32(BM, n_lo) : tc::idesc_bf16_f32(BM, n_lo);
+            const uint32_t idesc_hi = TF32 ? tc::idesc_tf32_f32(BM, n_hi) : tc::idesc_bf16_f32(BM, n_hi);
             uint32_t lt = 0;
             for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++lt) {
                 const int grp = lt % NGROUPS;
@@ -173,13 +177,15 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
                     const uint32_t a_addr = tc::smem_u32(smem + (size_t)s * stage_bytes);
                     const uint32_t w_addr = a_addr + A_BYTES;
 #pragma unroll
-                    for (int k = 0; k < BK / 16; ++k) {
+                    for (int k = 0; k < 4; ++k) {  // 4 x 32 bytes per chunk: UMMA_K = 16 bf16 or 8 tf32
                         const uint64_t ad = tc::smem_desc_sw128(a_addr + k * 32);
                         const uint64_t bd = tc::smem_desc_sw128(w_addr + k * 32);
-                        tc::umma_bf16(tacc, ad, bd, idesc_lo, (kc | k) != 0);
+                        if (TF32) tc::umma_tf32(tacc, ad, bd, idesc_lo, (kc | k) != 0);
+                        else tc::umma_bf16(tacc, ad, bd, idesc_lo, (kc | k) != 0);
                         if (p.NCP > 256) {
                             const uint64_t bd2 = tc::smem_desc_sw128(w_addr + 256 * 128 + k * 32);
-                            tc::umma_bf16(tacc + 256, ad, bd2, idesc_hi, (kc | k) != 0);
+                            if (TF32) tc::umma_tf32(tacc + 256, ad, bd2, idesc_hi, (kc | k) != 0);
+                            else tc::umma_bf16(tacc + 256, ad, bd2, idesc_hi, (kc | k) != 0);
                         }
                     }
                     tc::umma_commit(&empty_bar[s]);  // smem stage reusable once these MMAs have read it
@@ -231,24 +237,33 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
                     const int s = grp * spg + it % spg;
                     const uint32_t ph = (it / spg) & 1;
                     const uint32_t arow = tc::smem_u32(smem + (size_t)s * stage_bytes) + pt * 128;
-                    // all 64 loads of the chunk are issued before the first use (32 KB in flight per group)
-                    float v[64];
-                    const int cbase = kc * BK;
-                    if (valid && cbase + BK <= p.Cin) {
+                    // all loads of the chunk are issued before the first use (16-32 KB in flight per group)
+                    float v[BKE];
+                    const int cbase = kc * BKE;
+                    if (valid && cbase + BKE <= p.Cin) {
 #pragma unroll
-                        for (int e = 0; e < 64; ++e) v[e] = __ldg(src + (size_t)(cbase + e) * p.P);
+                        for (int e = 0; e < BKE; ++e) v[e] = __ldg(src + (size_t)(cbase + e) * p.P);
                     } else {
 #pragma unroll
-                        for (int e = 0; e < 64; ++e)
+                        for (int e = 0; e < BKE; ++e)
                             v[e] = (valid && cbase + e < p.Cin) ? __ldg(src + (size_t)(cbase + e) * p.P) : 0.f;
                     }
                     tc::mbar_wait(&empty_bar[s], ph ^ 1);
+                    if (TF32) {
 #pragma unroll
-                    for (int j = 0; j < 8; ++j)
-                        tc::st_shared_v4(arow + ((j ^ (pt & 7)) << 4), tc::pack_bf16x2(v[8 * j + 0], v[8 * j + 1]),
-                                         tc::pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
-                                         tc::pack_bf16x2(v[8 * j + 4], v[8 * j + 5]),
-                                         tc::pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+                        for (int j = 0; j < 8; ++j)
+                            tc::st_shared_v4(arow + ((j ^ (pt & 7)) << 4), tc::to_tf32(v[4 * j + 0]),
+                                             tc::to_tf32(v[4 * j + 1]), tc::to_tf32(v[4 * j + 2]),
+                                             tc::to_tf32(v[4 * j + 3]));
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j)
+                            tc::st_shared_v4(arow + ((j ^ (pt & 7)) << 4),
+                                             tc::pack_bf16x2(v[(8 * j + 0) % BKE], v[(8 * j + 1) % BKE]),
+                                             tc::pack_bf16x2(v[(8 * j + 2) % BKE], v[(8 * j + 3) % BKE]),
+                                             tc::pack_bf16x2(v[(8 * j + 4) % BKE], v[(8 * j + 5) % BKE]),
+                                             tc::pack_bf16x2(v[(8 * j + 6) % BKE], v[(8 * j + 7) % BKE]));
+                    }
                     tc::fence_proxy_async_smem();
                     tc::mbar_arrive(&full_bar[s]);
                 }
@@ -265,7 +280,7 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
                 for (int kc = 0; kc < p.kchunks; ++kc, ++it) {
                     const int s = grp * spg + it % spg;
                     const uint32_t ph = (it / spg) & 1;
-                    const int c0 = kc * BK + l8 * 8;
+                    const int c0 = kc * BKE + l8 * 8;
                     const bool cvalid = c0 < p.C1;  // C1 % 8 == 0: a lane's 8 channels are all valid or all padding
                     // rows of U for the 8 steps, issued up front
                     float4 u0[8], u1[8];
@@ -492,26 +507,29 @@ EncodeTiledFn get_encode_fn() {
     return fn;
 }
 
-// Tensor map over bf16 weights W (Cout rows, Kp columns, K-major), box = 64 columns x box_rows, 128B swizzle.
-int encode_weight_map(CUtensorMap *map, const void *W, int Cout, int Kp, int box_rows) {
+// Tensor map over K-major weights W (Cout rows, Kp columns; bf16, or fp32 read as tf32), box = one 128-byte span of
+// columns x box_rows, 128B swizzle.
+int encode_weight_map(CUtensorMap *map, const void *W, int Cout, int Kp, int box_rows, bool tf32) {
     EncodeTiledFn fn = get_encode_fn();
     if (!fn) return APB_E_UNSUPPORTED;
     const cuuint64_t gdim[2] = {(cuuint64_t)Kp, (cuuint64_t)Cout};
-    const cuuint64_t gstride[1] = {(cuuint64_t)Kp * 2};
-    const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+    const cuuint64_t gstride[1] = {(cuuint64_t)Kp * (tf32 ? 4 : 2)};
+    const cuuint32_t box[2] = {(cuuint32_t)(tf32 ? 32 : 64), (cuuint32_t)box_rows};
     const cuuint32_t estr[2] = {1, 1};
-    const CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(W), gdim, gstride, box, estr,
+    const CUresult r = fn(map, tf32 ? CU_TENSOR_MAP_DATA_TYPE_TFLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                          const_cast<void *>(W), gdim, gstride, box, estr,
                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS ? APB_OK : APB_E_INVALID;
 }
 
-template <int LOADER, int EPI>
+template <int LOADER, int EPI, bool TF32 = false>
 int launch_tc(TcParams p, const void *Wb, int Kp, cudaStream_t st) {
+    constexpr int BKE = TF32 ? 32 : 64;
     if (p.rows <= 0) return APB_OK;
-    if (p.Cout <= 0 || p.Cout > 512 || Kp <= 0 || (Kp % BK) != 0) return APB_E_UNSUPPORTED;
+    if (p.Cout <= 0 || p.Cout > 512 || Kp <= 0 || (Kp % BKE) != 0) return APB_E_UNSUPPORTED;
     if ((reinterpret_cast<uintptr_t>(Wb) & 15) != 0) return APB_E_INVALID;
-    p.kchunks = Kp / BK;
+    p.kchunks = Kp / BKE;
     p.NCP = (p.Cout + 15) / 16 * 16;
     p.wrows = p.NCP <= 256 ? p.NCP : 512;
     const int stage_bytes = A_BYTES + p.wrows * 128;
@@ -524,9 +542,9 @@ int launch_tc(TcParams p, const void *Wb, int Kp, cudaStream_t st) {
     p.stages = stages;
     const size_t smem = (size_t)stages * stage_bytes + extra;
     CUtensorMap map;
-    const int rc = encode_weight_map(&map, Wb, p.Cout, Kp, p.wrows > 256 ? 256 : p.wrows);
+    const int rc = encode_weight_map(&map, Wb, p.Cout, Kp, p.wrows > 256 ? 256 : p.wrows, TF32);
     if (rc != APB_OK) return rc;
-    auto kern = tc_rows_gemm_kernel<LOADER, EPI>;
+    auto kern = tc_rows_gemm_kernel<LOADER, EPI, TF32>;
     APB_CUDA(cudaFuncSetAttribute((const void *)kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long ntiles = (p.rows + BM - 1) / BM;
     const int grid = (int)(ntiles < APB_NUM_SMS ? ntiles : APB_NUM_SMS);
@@ -550,6 +568,20 @@ extern "C" int apb_pwconv_fwd_bf16(const float *x, const uint16_t *w_bf16, const
     p.scale = scale; p.shift = shift; p.relu = relu;
     p.Y = y;
     return launch_tc<LOAD_CHANNEL_MAJOR, EPI_STORE_CM>(p, w_bf16, Kp, (cudaStream_t)stream);
+}
+
+extern "C" int apb_pwconv_fwd_tf32(const float *x, const float *w, const float *scale, const float *shift, int relu,
+                                   float *y, int B, int Cin, int Cout, int P, int Kp, apb_stream_t stream) {
+    if (B < 0 || Cin <= 0 || Cout <= 0 || P < 0 || Kp < Cin) return APB_E_INVALID;
+    if (B == 0 || P == 0) return APB_OK;
+    if (!x || !w || !y || ((scale == nullptr) != (shift == nullptr))) return APB_E_INVALID;
+    TcParams p{};
+    p.rows = (long long)B * P;
+    p.Cout = Cout;
+    p.X = x; p.Cin = Cin; p.P = P;
+    p.scale = scale; p.shift = shift; p.relu = relu;
+    p.Y = y;
+    return launch_tc<LOAD_CHANNEL_MAJOR, EPI_STORE_CM, true>(p, w, Kp, (cudaStream_t)stream);
 }
 
 extern "C" int apb_sa_fused_fwd_bf16(const float *xyz, const float *new_xyz, const float *feat, const int32_t *idx,

@@ -4,10 +4,10 @@ nn.Conv1d / nn.Conv2d with kernel 1 is what every conv of the path is in the ref
 (openpoints/models/layers/conv.py:8-21: Conv1d/Conv2d wrappers; create_convblock1d/2d :24-103); torch runs them
 through cuDNN.  `TcConv1d` / `TcConv2d` keep the parameters, names and state_dict of nn.Conv{1,2}d and, when the
 backend switch is "tc", run
-    y  = W x (+b)            apb_pwconv_fwd_bf16   (bf16 operands, fp32 accumulate, tcgen05)
-    gx = W^T gy              apb_pwconv_fwd_bf16 on the transposed weights
+    y  = W x (+b)            apb_pwconv_fwd_tf32 | _bf16   (tf32 or bf16 operands, fp32 accumulate, tcgen05)
+    gx = W^T gy              the same kernel on the transposed weights
     gW = gy x^T              apb_pwconv_wgrad_tf32 (TF32, both operands TMA-fed)
-Numerics: 2e-2 relative (BASELINE.json north_star, "bf16 MLP path").  With the switch at "torch" (default) they
+Numerics: tf32 (default) ~1e-3 relative per layer; bf16 2e-2 (BASELINE.json north_star, "bf16 MLP path").  With the switch at "torch" (default) they
 are plain nn.Conv{1,2}d (strict fp32 parity tests use that).
 """
 import contextlib
@@ -20,7 +20,23 @@ from . import _cabi
 from .fused import pack_bf16
 
 _BACKEND = "torch"
+_PRECISION = "tf32"   # operands of y = W x and gx = W^T gy on the "tc" backend: "tf32" (default) or "bf16"
 _MAX_N = 512  # accumulator columns of one kernel call
+
+
+def set_conv_precision(name):
+    """'tf32' (10-bit mantissa operands: what the reference's cuDNN convs use by default on Ampere+) or 'bf16'
+    (BASELINE.json's "bf16 MLP path", 2e-2).  bf16 operand rounding flips enough max-pool / ReLU routing decisions
+    in PointNeXt to turn the weight gradients of the early stages ~40 degrees (cos 0.75 vs fp32, measured in
+    scripts/dbg_tc2.py against an exact torch emulation), tf32 keeps cos > 0.999, at the same HBM-bound speed."""
+    global _PRECISION
+    if name not in ("tf32", "bf16"):
+        raise ValueError(name)
+    _PRECISION = name
+
+
+def get_conv_precision():
+    return _PRECISION
 
 
 def set_conv_backend(name):
@@ -45,19 +61,31 @@ def conv_backend(name):
         set_conv_backend(prev)
 
 
+def pack_f32(W):
+    """(Cout, Cin) f32 -> (Cout, Kp) f32, K-major, zero padded to a multiple of 32 columns."""
+    cout, cin = W.shape
+    kp = (cin + 31) // 32 * 32
+    if kp == cin:
+        return W.contiguous(), kp
+    out = torch.zeros((cout, kp), dtype=torch.float32, device=W.device)
+    out[:, :cin] = W
+    return out, kp
+
+
 def _gemm_rows(x, w2d, bias, B, cin, cout, P):
-    """y (B,cout,P) = w2d (cout,cin) . x (B,cin,P) (+bias) through apb_pwconv_fwd_bf16, splitting cout > 512."""
+    """y (B,cout,P) = w2d (cout,cin) . x (B,cin,P) (+bias) through apb_pwconv_fwd_{tf32,bf16}, splitting cout > 512."""
     outs = []
+    entry = "apb_pwconv_fwd_tf32" if _PRECISION == "tf32" else "apb_pwconv_fwd_bf16"
     for c0 in range(0, cout, _MAX_N):
         c1 = min(cout, c0 + _MAX_N)
-        wb, kp = pack_bf16(w2d[c0:c1])
+        wb, kp = (pack_f32 if _PRECISION == "tf32" else pack_bf16)(w2d[c0:c1])
         y = torch.empty((B, c1 - c0, P), dtype=torch.float32, device=x.device)
         if bias is not None:
             scale = torch.ones(c1 - c0, dtype=torch.float32, device=x.device)
             shift = bias[c0:c1].contiguous().float()
         else:
             scale = shift = None
-        _cabi.call("apb_pwconv_fwd_bf16", [x, wb, scale, shift, 0, y, B, cin, c1 - c0, P, kp], x.device)
+        _cabi.call(entry, [x, wb, scale, shift, 0, y, B, cin, c1 - c0, P, kp], x.device)
         outs.append(y)
     return outs[0] if len(outs) == 1 else torch.cat(outs, dim=1)
 

@@ -55,7 +55,13 @@ def allreduce_grads(params, bucket=None):
         g.copy_(s)
 
 
-def feedback_loss(classifier, criterion, data_real, data_fake, epoch, cfg):
+def hard_ratio(epoch, cfg):
+    """rho of the perception-guidance loss, linear in the epoch (ganloss_cls.py:53-54)."""
+    ap = cfg["adaptpoint_params"]
+    return ap["hardratio_s"] + (ap["hardratio"] - ap["hardratio_s"]) * epoch / cfg["epochs"]
+
+
+def feedback_loss(classifier, criterion, data_real, data_fake, rho):
     """|1 - exp(L_fake - rho * L_real)| with the classifier in eval mode but inside autograd
     (ganloss_cls.py:31-65)."""
     classifier.eval()
@@ -63,8 +69,6 @@ def feedback_loss(classifier, criterion, data_real, data_fake, epoch, cfg):
     pred_real = classifier(data_real)
     label = data_real["y"].long()
     loss_fake, loss_real = criterion(pred_fake, label), criterion(pred_real, label)
-    ap = cfg["adaptpoint_params"]
-    rho = ap["hardratio_s"] + (ap["hardratio"] - ap["hardratio_s"]) * epoch / cfg["epochs"]
     return torch.abs(1 - torch.exp(loss_fake - rho * loss_real)).mean()
 
 
@@ -89,30 +93,50 @@ class AdaptPointTrainer:
                 for t in list(net.parameters()) + list(net.buffers()):
                     dist.broadcast(t.data, 0)
         ap = self.cfg["adaptpoint_params"]
+        cap = self.device.type == "cuda"      # device-side step counters: required inside a CUDA graph
         self.opt_c = torch.optim.AdamW(self.classifier.parameters(), lr=self.cfg["lr"],
-                                       weight_decay=self.cfg["weight_decay"])
-        self.opt_g = torch.optim.Adam(self.generator.parameters(), lr=ap["lr_generator"], betas=(ap["b1"], ap["b2"]))
+                                       weight_decay=self.cfg["weight_decay"], capturable=cap)
+        self.opt_g = torch.optim.Adam(self.generator.parameters(), lr=ap["lr_generator"], betas=(ap["b1"], ap["b2"]),
+                                      capturable=cap)
         self.opt_d = torch.optim.Adam(self.discriminator.parameters(), lr=ap["lr_discriminator"],
-                                      betas=(ap["b1"], ap["b2"]))
+                                      betas=(ap["b1"], ap["b2"]), capturable=cap)
         self.criterion_gan = nn.BCELoss()
         self.criterion = SmoothCrossEntropy(label_smoothing=self.cfg["label_smoothing"])
         self.pointwolf = PointWOLF_classversion(**self.cfg["pointwolf"])
         self.epoch = 0
+        self._rho = torch.tensor(float(hard_ratio(0, self.cfg)), device=self.device)   # device scalar: graph-safe
+        self._graph = None
 
     # -- train_autoaug.py:131-207 ---------------------------------------------------------------------------
-    def gan_iteration(self, points, label):
+    def set_epoch(self, epoch):
+        self.epoch = epoch
+        self._rho.fill_(float(hard_ratio(epoch, self.cfg)))
+
+    def draw_noise(self, B, n_loader_points):
+        """All host-RNG draws of one step, in the order the reference makes them: PointWOLF (pointwolf.py:113-131),
+        the imitator's dropout/axes (generator_component4_15.py:245-247,308), the resampling subset
+        (train_autoaug.py:497, np.random.choice)."""
+        npoints = self.cfg["num_points"]
+        noise = {"wolf": self.pointwolf.draw(B), "gen": self.generator.draw(B)}
+        if n_loader_points > npoints:
+            point_all = min({1024: 1200, 4096: 4800, 8192: 8192}[npoints], n_loader_points)
+            noise["keep"] = torch.randperm(point_all)[:npoints]
+        return noise
+
+    def gan_iteration(self, points, label, noise=None):
         """points (B,N,C>=4) loader-shaped, label (B,).  Returns (generated batch (B,N,C), g_loss, d_loss)."""
         cfg = self.cfg
         G, D, C = self.generator, self.discriminator, self.classifier
         G.train(); D.train(); C.eval()
         points_clone = points.clone()
         inp = points[:, :, :3].contiguous()
-        self.pointwolf(inp)                                     # the reference runs it for its h5 dump (:143)
+        noise = noise or {}
+        self.pointwolf(inp, noise.get("wolf"))                  # the reference runs it for its h5 dump (:143)
         B = inp.size(0)
         real_label = torch.full((B, 1), 0.9, device=inp.device)
         fake_label = torch.full((B, 1), 0.1, device=inp.device)
 
-        _, gen = G(inp)
+        _, gen = G(inp, noise.get("gen"))
         g_loss_raw = self.criterion_gan(D(gen), real_label)
         fake_pts = torch.cat([gen, points[:, :, 3:]], dim=-1)   # `points[:, :, :3] = gen_imgs` (:152)
         nc = cfg["in_channels"]
@@ -123,7 +147,7 @@ class AdaptPointTrainer:
         ratio = cfg.get("feedbackloss_ratio", 1)
         g_loss = g_loss_raw
         if ratio > 0:
-            g_loss = g_loss_raw + feedback_loss(C, self.criterion, data_real, data_fake, self.epoch, cfg) * ratio
+            g_loss = g_loss_raw + feedback_loss(C, self.criterion, data_real, data_fake, self._rho) * ratio
         self.opt_g.zero_grad()
         g_loss.backward()
         allreduce_grads(list(G.parameters()))
@@ -140,7 +164,7 @@ class AdaptPointTrainer:
         return fake_pts.detach(), g_loss.detach(), d_loss.detach()
 
     # -- train_autoaug.py:474-506 ---------------------------------------------------------------------------
-    def classifier_iteration(self, points, target):
+    def classifier_iteration(self, points, target, keep=None):
         cfg = self.cfg
         model = self.classifier
         model.train()
@@ -149,7 +173,9 @@ class AdaptPointTrainer:
             point_all = {1024: 1200, 4096: 4800, 8192: 8192}[npoints]
             point_all = min(point_all, points.size(1))
             fps_idx = ops.furthest_point_sample(points[:, :, :3].contiguous(), point_all)
-            keep = torch.randperm(point_all)[:npoints].to(points.device)  # np.random.choice(point_all, npoints, False)
+            if keep is None:                                    # np.random.choice(point_all, npoints, False)
+                keep = torch.randperm(point_all)[:npoints]
+            keep = keep.to(points.device)
             fps_idx = fps_idx[:, keep]
             points = torch.gather(points, 1, fps_idx.unsqueeze(-1).long().expand(-1, -1, points.shape[-1]))
         data = {"pos": points[:, :, :3].contiguous(),
@@ -163,9 +189,59 @@ class AdaptPointTrainer:
         model.zero_grad()
         return logits.detach(), loss.detach()
 
-    def step(self, points, label):
-        """One full AdaptPoint step on a loader-shaped batch.  Returns (cls_loss, g_loss, d_loss) tensors."""
+    def _step_impl(self, points, label, noise):
         with tcconv.conv_backend(self.conv_backend):
-            fake, g_loss, d_loss = self.gan_iteration(points, label)
-            _, loss = self.classifier_iteration(fake, label)
+            fake, g_loss, d_loss = self.gan_iteration(points, label, noise)
+            _, loss = self.classifier_iteration(fake, label, noise.get("keep"))
         return loss, g_loss, d_loss
+
+    def step(self, points, label):
+        """One full AdaptPoint step on a loader-shaped batch.  Returns (cls_loss, g_loss, d_loss) tensors.
+        After `capture_graph`, the whole step (three forward/backward passes, gradient all-reduces, three optimizer
+        updates: ~3000 kernel launches) is ONE CUDA-graph replay; only the host-RNG draws stay on the host."""
+        noise = self.draw_noise(points.shape[0], points.shape[1])
+        if self._graph is None:
+            return self._step_impl(points, label, noise)
+        self._g_points.copy_(points, non_blocking=True)
+        self._g_label.copy_(label, non_blocking=True)
+        _copy_tree(self._g_noise, noise)
+        self._graph.replay()
+        return self._g_out
+
+    def capture_graph(self, points, label, warmup=3):
+        """Capture `step` for this batch shape into a CUDA graph (static input / noise buffers).  The warm-up
+        iterations are real training steps."""
+        if self.device.type != "cuda":
+            raise RuntimeError("CUDA graphs need a CUDA device")
+        self._graph = None
+        self._g_points, self._g_label = points.clone(), label.clone()
+        self._g_noise = _to_device_tree(self.draw_noise(points.shape[0], points.shape[1]), self.device)
+        side = torch.cuda.Stream(device=self.device)
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                _copy_tree(self._g_noise, self.draw_noise(points.shape[0], points.shape[1]))
+                self._step_impl(self._g_points, self._g_label, self._g_noise)
+        torch.cuda.current_stream(self.device).wait_stream(side)
+        torch.cuda.synchronize(self.device)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            out = self._step_impl(self._g_points, self._g_label, self._g_noise)
+        self._g_out = out
+        self._graph = graph
+        return graph
+
+
+def _to_device_tree(tree, device):
+    if isinstance(tree, dict):
+        return {k: _to_device_tree(v, device) for k, v in tree.items()}
+    return tree.to(device)
+
+
+def _copy_tree(dst, src):
+    """Copy host draws into the graph's static device buffers (stream-ordered before the replay)."""
+    for k, v in src.items():
+        if isinstance(v, dict):
+            _copy_tree(dst[k], v)
+        else:
+            dst[k].copy_(v, non_blocking=True)

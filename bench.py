@@ -89,6 +89,12 @@ def alg_bytes(name, a):
     if name == "apb_deform_mask_bwd_f32":
         B, N, M = a
         return 4.0 * B * (3 * N + N + 3 * N + N)
+    if name in ("apb_pwconv_fwd_bf16", "apb_pwconv_fwd_tf32"):
+        _relu, B, Cin, Cout, P, _kp = a
+        return 4.0 * B * P * (Cin + Cout)
+    if name == "apb_pwconv_wgrad_tf32":
+        B, Cin, Cout, P = a
+        return 4.0 * B * P * (Cin + Cout)
     if name.startswith("apb_sa_fused"):
         return None
     return None
@@ -200,7 +206,7 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
     _cabi.load()
 
-    tr = AdaptPointTrainer(device=dev, seed=0)
+    tr = AdaptPointTrainer(device=dev, seed=0, conv_backend=args.conv)
     pts_h, y_h = loader_batch(B_PER_GPU, N_POINTS, 100 + rank)
     pts_pin, y_pin = pts_h.pin_memory(), y_h.pin_memory()
     loss_pin = torch.empty(3, dtype=torch.float32).pin_memory()
@@ -231,24 +237,36 @@ def run_ours(args):
         tr.step(pts_d.clone(), y_d)
 
     def e2e_step():
-        p = pts_pin.to(dev, non_blocking=True)
-        y = y_pin.to(dev, non_blocking=True)
-        losses = tr.step(p, y)
+        if tr._graph is not None:       # the graph's static input buffers are filled straight from pinned memory
+            losses = tr.step(pts_pin, y_pin)
+        else:
+            losses = tr.step(pts_pin.to(dev, non_blocking=True), y_pin.to(dev, non_blocking=True))
         loss_pin.copy_(torch.stack([l.float() for l in losses]), non_blocking=True)
         torch.cuda.current_stream().synchronize()
 
     for _ in range(max(args.warmup, 3)):
         resident_step()
+    # per-kernel CUDA-event trace of our C-ABI launches over `trace_steps` eager steps (events cannot be recorded
+    # inside a graph capture); the roofline object below is computed from it
+    trace_steps = min(args.steps, 3)
+    _cabi.TRACE = []
+    ms_trace = timed(resident_step, trace_steps)
+    trace, _cabi.TRACE = _cabi.TRACE, None
+    _cabi.LAUNCHES = 0
+    if args.graph:
+        tr.capture_graph(pts_d, y_d, warmup=3)        # launches counted during the capture = launches per replay
+        launches_per_step = _cabi.LAUNCHES // 4       # 3 warm-up steps + 1 captured step
+        resident_step()
+    else:
+        resident_step()
+        launches_per_step = _cabi.LAUNCHES
     e2e_step()
 
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    _cabi.LAUNCHES = 0
-    _cabi.TRACE = []
     ms_total = timed(resident_step, args.steps)
-    launches = _cabi.LAUNCHES
-    trace, _cabi.TRACE = _cabi.TRACE, None
+    launches = launches_per_step * args.steps
     ms_e2e = timed(e2e_step, args.steps)
     clocks = sampler.stop() if rank == 0 else None
 
@@ -264,7 +282,10 @@ def run_ours(args):
             d = agg.setdefault((name, a), [0, 0.0])
             d[0] += 1
             d[1] += e0.elapsed_time(e1)
-        ours_ms = sum(v[1] for v in agg.values())
+        ours_ms = sum(v[1] for v in agg.values()) * args.steps / trace_steps     # scaled to the timed region
+        for v in agg.values():
+            v[0] = v[0] * args.steps // trace_steps
+            v[1] = v[1] * args.steps / trace_steps
         table = sorted(((k, v) for k, v in agg.items()), key=lambda kv: -kv[1][1])
         (dname, dargs), (dcount, dms) = table[0]
         ab = alg_bytes(dname, dargs)
@@ -276,8 +297,15 @@ def run_ours(args):
         out = {
             "metric": METRIC, "value": round(samples / (ms_total / 1e3), 2), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms_total / args.steps, 3),
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "tf32" if args.conv == "tc" else "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "global_batch": world * B_PER_GPU, "parallelism": f"dp{world}",
+                       "precision": ("1x1 convs: tf32 operands (fwd, dgrad, wgrad), fp32 accumulate, tcgen05 (= the reference's "
+                                     "default cuDNN allow_tf32); "
+                                     "everything else fp32" if args.conv == "tc" else "strict fp32 (cuDNN, TF32 off)"),
+                       "cuda_graph": bool(args.graph),
+                       "kernel_trace": f"C-ABI launches timed with CUDA events over {trace_steps} eager steps before "
+                                       "the timed region (same kernels the graph replays), scaled to K steps",
                        "l2": "256 MB flush write between timed steps (outside the per-step event pairs)",
                        "timing": "per-step CUDA events on the launching stream, max over ranks"},
             "e2e": {"value": round(samples / (ms_e2e / 1e3), 2), "unit": UNIT,
@@ -311,6 +339,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--conv", default="tc", choices=["tc", "torch"], help="1x1-conv backend (tcgen05 kernels / cuDNN fp32)")
+    ap.add_argument("--no-graph", dest="graph", action="store_false", help="eager launches instead of one CUDA graph")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

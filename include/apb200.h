@@ -114,6 +114,12 @@ int apb_deform_mask_bwd_f32(const float *xyz, const float *anchor, const float *
 int apb_pwconv_fwd_bf16(const float *x, const uint16_t *w_bf16, const float *scale, const float *shift, int relu,
                         float *y, int B, int Cin, int Cout, int P, int Kp, apb_stream_t stream);
 
+/* Same layer with TF32 operands (fp32 inputs rounded to tf32 by the producers / the TMA unit, fp32 accumulate):
+ *   w (Cout,Kp) f32 K-major, columns >= Cin zero, Kp % 32 == 0.  This is the training-path precision: it equals the
+ * reference's default cuDNN behaviour on Ampere+ (torch.backends.cudnn.allow_tf32 = True). */
+int apb_pwconv_fwd_tf32(const float *x, const float *w, const float *scale, const float *shift, int relu, float *y,
+                        int B, int Cin, int Cout, int P, int Kp, apb_stream_t stream);
+
 /* Weight gradient of the 1x1 convolution above (TF32 tcgen05, both operands TMA-fed):
  *   grad_w[co,ci] += sum_{b,p} grad_y[b,co,p] * x[b,ci,p];  grad_w (Cout,Cin) f32 pre-zeroed by the caller.
  *   grad_y (B,Cout,P), x (B,Cin,P) f32 channel-major, P % 4 == 0 (else APB_E_UNSUPPORTED).

@@ -24,8 +24,10 @@ def _rel(got, want):
     (2, 64, 3, (1000,), False),        # tiny Cout
     (2, 16, 24, (333,), True),         # P % 4 != 0: weight gradient falls back to einsum
 ])
-def test_pointwise_conv_fwd_bwd(cuda_dev, B, cin, cout, shape, bias):
+@pytest.mark.parametrize("prec,tol", [("tf32", 3e-3), ("bf16", TOL)])
+def test_pointwise_conv_fwd_bwd(cuda_dev, B, cin, cout, shape, bias, prec, tol):
     from adaptpoint_b200 import tcconv
+    tcconv.set_conv_precision(prec)
     gen = torch.Generator().manual_seed(cin + cout)
     Conv = tcconv.TcConv2d if len(shape) == 2 else tcconv.TcConv1d
     conv = Conv(cin, cout, 1, bias=bias).to(cuda_dev)
@@ -39,10 +41,11 @@ def test_pointwise_conv_fwd_bwd(cuda_dev, B, cin, cout, shape, bias):
     with tcconv.conv_backend("tc"):
         got = conv(x)
         got.backward(gy)
+    tcconv.set_conv_precision("tf32")
     assert got.shape == want.shape
-    assert _rel(got, want) < TOL
-    assert _rel(x.grad, ref[0]) < TOL
-    assert _rel(conv.weight.grad, ref[1]) < TOL
+    assert _rel(got, want) < tol
+    assert _rel(x.grad, ref[0]) < tol
+    assert _rel(conv.weight.grad, ref[1]) < 5e-3       # wgrad is tf32 in both modes
     if bias:
         assert _rel(conv.bias.grad, ref[2]) < 1e-4
 
@@ -79,12 +82,13 @@ def test_model_step_tc_vs_fp32(cuda_dev):
             loss.backward()
         grads = {n: p.grad.clone() for n, p in model.named_parameters() if p.grad is not None}
         outs[backend] = (logits.detach().clone(), loss.item(), grads)
-    assert abs(outs["tc"][1] - outs["torch"][1]) < 2e-2 * max(1.0, abs(outs["torch"][1]))
-    assert _rel(outs["tc"][0], outs["torch"][0]) < 5e-2
-    # gradients pass through six bf16 stages + training-mode BatchNorm: compare direction, not digits
+    assert abs(outs["tc"][1] - outs["torch"][1]) < 2e-3 * max(1.0, abs(outs["torch"][1]))
+    assert _rel(outs["tc"][0], outs["torch"][0]) < 5e-2   # head BatchNorm1d over 8 samples amplifies ~10x
+    # weight gradients through 12 stacked layers, training-mode BatchNorm, max-pool routing: tf32 operands keep the
+    # direction (bf16 operands do not: cos ~0.75, see tcconv.set_conv_precision)
     for n, g in outs["torch"][2].items():
         gt = outs["tc"][2][n]
         if g.numel() < 64 or g.norm() < 1e-6:
             continue
         cos = torch.nn.functional.cosine_similarity(g.flatten(), gt.flatten(), dim=0).item()
-        assert cos > 0.98, (n, cos)
+        assert cos > 0.995, (n, cos)
