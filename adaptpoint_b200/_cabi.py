@@ -14,6 +14,7 @@ _LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libapb200.
 _lib = None
 
 _i, _f, _p = ctypes.c_int, ctypes.c_float, ctypes.c_void_p
+_d, _ll = ctypes.c_double, ctypes.c_longlong
 
 # name -> argtypes (all return int status unless noted)
 _SIGNATURES = {
@@ -32,6 +33,12 @@ _SIGNATURES = {
     "apb_pwconv_fwd_bf16": [_p, _p, _p, _p, _i, _p, _i, _i, _i, _i, _i, _p],
     "apb_pwconv_fwd_tf32": [_p, _p, _p, _p, _i, _p, _i, _i, _i, _i, _i, _p],
     "apb_pwconv_wgrad_tf32": [_p, _p, _p, _i, _i, _i, _i, _p],
+    "apb_bn_stats_f32": [_p, _p, _i, _i, _ll, _p],
+    "apb_bn_apply_f32": [_p, _p, _p, _p, _f, _d, _i, _p, _p, _p, _p, _p, _f, _i, _i, _ll, _p],
+    "apb_bn_bwd_reduce_f32": [_p, _p, _p, _p, _p, _p, _i, _i, _ll, _p],
+    "apb_bn_bwd_apply_f32": [_p, _p, _p, _p, _p, _p, _p, _d, _p, _i, _i, _ll, _p],
+    "apb_kmax_stats_f32": [_p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
+    "apb_bnmax_bwd_f32": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
     "apb_sa_fused_fwd_bf16": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _i, _p, _p,
                               _i, _i, _i, _i, _i, _i, _i, _i, _i, _p],
 }

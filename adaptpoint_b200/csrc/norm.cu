@@ -205,3 +205,162 @@ __global__ void __launch_bounds__(NT) bn_bwd_apply_kernel(const float *__restric
         }
     }
 }
+
+// ---- BatchNorm -> max over K: statistics + per-(b,c,m) extrema in one read pass ------------------------------------
+// y (B, C, M, K): thread <-> one (b,c,m) row of K contiguous values.
+// vmax/vmin (B,C,M) f32; arg (B,C,M) int32 = argmax | (argmin << 16), first index on ties; stats[c] += (sum, sumsq).
+__global__ void __launch_bounds__(NT) kmax_stats_kernel(const float *__restrict__ y, float *__restrict__ vmax,
+                                                        float *__restrict__ vmin, int32_t *__restrict__ arg,
+                                                        double *__restrict__ stats, int C, int M, int K) {
+    const int c = blockIdx.y, b = blockIdx.z;
+    const int m = blockIdx.x * NT + threadIdx.x;
+    float s = 0.f, q = 0.f;
+    if (m < M) {
+        const size_t rowi = ((size_t)b * C + c) * M + m;
+        const float *row = y + rowi * K;
+        float mx = -INFINITY, mn = INFINITY;
+        int ax = 0, an = 0;
+        if ((K & 3) == 0 && (reinterpret_cast<uintptr_t>(row) & 15) == 0) {
+            for (int k = 0; k < K; k += 4) {
+                const float4 v = apb_ld_nc_f4(row + k);
+                const float e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    s += e[j];
+                    q += e[j] * e[j];
+                    if (e[j] > mx) { mx = e[j]; ax = k + j; }
+                    if (e[j] < mn) { mn = e[j]; an = k + j; }
+                }
+            }
+        } else {
+            for (int k = 0; k < K; ++k) {
+                const float e = __ldg(row + k);
+                s += e;
+                q += e * e;
+                if (e > mx) { mx = e; ax = k; }
+                if (e < mn) { mn = e; an = k; }
+            }
+        }
+        vmax[rowi] = mx;
+        vmin[rowi] = mn;
+        arg[rowi] = ax | (an << 16);
+    }
+    if (stats) {
+        block_sum2(s, q);
+        if (threadIdx.x == 0) {
+            atomicAdd(stats + 2 * c, (double)s);
+            atomicAdd(stats + 2 * c + 1, (double)q);
+        }
+    }
+}
+
+// dy[b,c,m,k] = gsel[b,c,m] * [k == arg[b,c,m]] + a[c] + bcoef[c] * y[b,c,m,k]
+__global__ void __launch_bounds__(NT) bnmax_bwd_kernel(const float *__restrict__ y, const float *__restrict__ gsel,
+                                                       const int32_t *__restrict__ arg, const float *__restrict__ a,
+                                                       const float *__restrict__ bcoef, float *__restrict__ dy, int C,
+                                                       int M, int K) {
+    const int c = blockIdx.y, b = blockIdx.z;
+    const int m = blockIdx.x * NT + threadIdx.x;
+    if (m >= M) return;
+    const size_t rowi = ((size_t)b * C + c) * M + m;
+    const float *row = y + rowi * K;
+    float *out = dy + rowi * K;
+    const float g = gsel[rowi], a0 = a ? a[c] : 0.f, b0 = bcoef ? bcoef[c] : 0.f;
+    const int sel = arg[rowi];
+    if ((K & 3) == 0 && ((reinterpret_cast<uintptr_t>(row) | reinterpret_cast<uintptr_t>(out)) & 15) == 0) {
+        for (int k = 0; k < K; k += 4) {
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (bcoef) v = apb_ld_nc_f4(row + k);
+            v.x = fmaf(b0, v.x, a0) + (sel == k + 0 ? g : 0.f);
+            v.y = fmaf(b0, v.y, a0) + (sel == k + 1 ? g : 0.f);
+            v.z = fmaf(b0, v.z, a0) + (sel == k + 2 ? g : 0.f);
+            v.w = fmaf(b0, v.w, a0) + (sel == k + 3 ? g : 0.f);
+            *reinterpret_cast<float4 *>(out + k) = v;
+        }
+    } else {
+        for (int k = 0; k < K; ++k) out[k] = fmaf(b0, bcoef ? __ldg(row + k) : 0.f, a0) + (sel == k ? g : 0.f);
+    }
+}
+
+bool grid_ok(int B, int C) { return B <= 65535 && C <= 65535; }
+
+}  // namespace
+
+extern "C" int apb_bn_stats_f32(const float *x, double *stats, int B, int C, long long P, apb_stream_t stream) {
+    if (B < 0 || C < 0 || P < 0) return APB_E_INVALID;
+    if (B == 0 || C == 0 || P == 0) return APB_OK;
+    if (!x || !stats) return APB_E_INVALID;
+    if (!grid_ok(B, C)) return APB_E_UNSUPPORTED;
+    dim3 grid(apb_div_up(P, CHUNK), C, B);
+    bn_stats_kernel<<<grid, NT, 0, (cudaStream_t)stream>>>(x, stats, C, P);
+    APB_CHECK_LAUNCH();
+    return APB_OK;
+}
+
+extern "C" int apb_bn_apply_f32(const float *x, const double *stats, const float *gamma, const float *beta, float eps,
+                                double count, int relu, float *y, float *save_mean, float *save_rstd,
+                                float *running_mean, float *running_var, float momentum, int B, int C, long long P,
+                                apb_stream_t stream) {
+    if (B < 0 || C < 0 || P < 0 || count < 1.0) return APB_E_INVALID;
+    if (B == 0 || C == 0 || P == 0) return APB_OK;
+    if (!x || !stats || !gamma || !beta || !y || !save_mean || !save_rstd) return APB_E_INVALID;
+    if ((running_mean == nullptr) != (running_var == nullptr)) return APB_E_INVALID;
+    if (!grid_ok(B, C)) return APB_E_UNSUPPORTED;
+    BnApplyParams p{x, y, stats, gamma, beta, eps, 1.0 / count, count > 1.0 ? count / (count - 1.0) : 1.0, relu,
+                    save_mean, save_rstd, running_mean, running_var, momentum, C, P};
+    dim3 grid(apb_div_up(P, CHUNK), C, B);
+    bn_apply_kernel<<<grid, NT, 0, (cudaStream_t)stream>>>(p);
+    APB_CHECK_LAUNCH();
+    return APB_OK;
+}
+
+extern "C" int apb_bn_bwd_reduce_f32(const float *x, const float *dy, const float *y_relu, const float *save_mean,
+                                     const float *save_rstd, double *stats2, int B, int C, long long P,
+                                     apb_stream_t stream) {
+    if (B < 0 || C < 0 || P < 0) return APB_E_INVALID;
+    if (B == 0 || C == 0 || P == 0) return APB_OK;
+    if (!x || !dy || !save_mean || !save_rstd || !stats2) return APB_E_INVALID;
+    if (!grid_ok(B, C)) return APB_E_UNSUPPORTED;
+    dim3 grid(apb_div_up(P, CHUNK), C, B);
+    bn_bwd_reduce_kernel<<<grid, NT, 0, (cudaStream_t)stream>>>(x, dy, y_relu, save_mean, save_rstd, stats2, C, P);
+    APB_CHECK_LAUNCH();
+    return APB_OK;
+}
+
+extern "C" int apb_bn_bwd_apply_f32(const float *x, const float *dy, const float *y_relu, const float *save_mean,
+                                    const float *save_rstd, const float *gamma, const double *stats2, double count,
+                                    float *dx, int B, int C, long long P, apb_stream_t stream) {
+    if (B < 0 || C < 0 || P < 0 || count < 1.0) return APB_E_INVALID;
+    if (B == 0 || C == 0 || P == 0) return APB_OK;
+    if (!x || !dy || !save_mean || !save_rstd || !gamma || !stats2 || !dx) return APB_E_INVALID;
+    if (!grid_ok(B, C)) return APB_E_UNSUPPORTED;
+    dim3 grid(apb_div_up(P, CHUNK), C, B);
+    bn_bwd_apply_kernel<<<grid, NT, 0, (cudaStream_t)stream>>>(x, dy, y_relu, save_mean, save_rstd, gamma, stats2,
+                                                               1.0 / count, dx, C, P);
+    APB_CHECK_LAUNCH();
+    return APB_OK;
+}
+
+extern "C" int apb_kmax_stats_f32(const float *y, float *vmax, float *vmin, int32_t *arg, double *stats, int B, int C,
+                                  int M, int K, apb_stream_t stream) {
+    if (B < 0 || C < 0 || M < 0 || K <= 0 || K > 32767) return APB_E_INVALID;
+    if (B == 0 || C == 0 || M == 0) return APB_OK;
+    if (!y || !vmax || !vmin || !arg) return APB_E_INVALID;
+    if (!grid_ok(B, C)) return APB_E_UNSUPPORTED;
+    dim3 grid(apb_div_up(M, NT), C, B);
+    kmax_stats_kernel<<<grid, NT, 0, (cudaStream_t)stream>>>(y, vmax, vmin, arg, stats, C, M, K);
+    APB_CHECK_LAUNCH();
+    return APB_OK;
+}
+
+extern "C" int apb_bnmax_bwd_f32(const float *y, const float *gsel, const int32_t *arg, const float *a,
+                                 const float *bcoef, float *dy, int B, int C, int M, int K, apb_stream_t stream) {
+    if (B < 0 || C < 0 || M < 0 || K <= 0) return APB_E_INVALID;
+    if (B == 0 || C == 0 || M == 0) return APB_OK;
+    if (!gsel || !arg || !dy || (bcoef && !y)) return APB_E_INVALID;
+    if (!grid_ok(B, C)) return APB_E_UNSUPPORTED;
+    dim3 grid(apb_div_up(M, NT), C, B);
+    bnmax_bwd_kernel<<<grid, NT, 0, (cudaStream_t)stream>>>(y, gsel, arg, a, bcoef, dy, C, M, K);
+    APB_CHECK_LAUNCH();
+    return APB_OK;
+}

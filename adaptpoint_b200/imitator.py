@@ -24,6 +24,7 @@ import torch.nn.functional as F
 from torch.autograd import Function
 
 from . import _cabi, ops
+from .norm import ConvBlock, TcBatchNorm1d
 from .tcconv import TcConv1d, TcConv2d
 
 
@@ -145,8 +146,8 @@ class ConvBNReLU1D(nn.Module):
         if activation.lower() != "relu":
             raise NotImplementedError(activation)
         self.act = nn.ReLU(inplace=True)
-        self.net = nn.Sequential(TcConv1d(in_channels, out_channels, kernel_size, bias=bias),
-                                 nn.BatchNorm1d(out_channels), self.act)
+        self.net = ConvBlock(TcConv1d(in_channels, out_channels, kernel_size, bias=bias),
+                             TcBatchNorm1d(out_channels), self.act)
 
     def forward(self, x):
         return self.net(x)
@@ -204,8 +205,8 @@ class Anchor_selfattention(nn.Module):
         self.dim, self.head_num = dim, head_num
         self.head_dim = int(dim // head_num)
         self.to_qkv = nn.Linear(dim, dim * 3, bias=False)
-        self.pos_embedding = nn.Sequential(TcConv1d(3, dim, 1), nn.BatchNorm1d(dim))
-        self.res = nn.Sequential(TcConv1d(dim, dim, 1), nn.BatchNorm1d(dim))
+        self.pos_embedding = nn.Sequential(TcConv1d(3, dim, 1), TcBatchNorm1d(dim))
+        self.res = nn.Sequential(TcConv1d(dim, dim, 1), TcBatchNorm1d(dim))
 
     def forward(self, x, xyz=None):
         """x (B,M,C), xyz (B,M,3) -> (B,M,C)."""
@@ -225,8 +226,8 @@ class Producefactor(nn.Module):
     def __init__(self, kneighbors, out_channels):
         super().__init__()
         self.keighbors, self.out_channels = kneighbors, out_channels
-        self.global_layer = nn.Sequential(TcConv1d(3, out_channels, 1, bias=False), nn.BatchNorm1d(out_channels))
-        self.prob_head = nn.Sequential(TcConv1d(out_channels * 2, 9, 1, bias=False), nn.BatchNorm1d(9))
+        self.global_layer = nn.Sequential(TcConv1d(3, out_channels, 1, bias=False), TcBatchNorm1d(out_channels))
+        self.prob_head = nn.Sequential(TcConv1d(out_channels * 2, 9, 1, bias=False), TcBatchNorm1d(9))
         self.anchor_selfattention = Anchor_selfattention(dim=out_channels, head_num=4)
 
     def forward(self, a_points, sa_x, sa_xyz, xyz_raw=None):
@@ -276,9 +277,9 @@ class SAComponent(nn.Module):
             PointNetFeaturePropagation(channels[-(i + 1)] + channels[-(i + 2)], channels[-(i + 2)], bias=bias,
                                        activation=activation) for i in range(self.stages)])
         self.localfeat_mask_selfattention = Anchor_selfattention(dim=embed_dim, head_num=4)
-        self.extract_local_feat_masking = nn.Sequential(TcConv1d(embed_dim, 3, 1, bias=False), nn.BatchNorm1d(3))
-        self.extract_global_feat_masking = nn.Sequential(TcConv1d(last, 3, 1, bias=False), nn.BatchNorm1d(3))
-        self.fuse_masking = nn.Sequential(TcConv1d(6, 2, 1, bias=False), nn.BatchNorm1d(2))
+        self.extract_local_feat_masking = nn.Sequential(TcConv1d(embed_dim, 3, 1, bias=False), TcBatchNorm1d(3))
+        self.extract_global_feat_masking = nn.Sequential(TcConv1d(last, 3, 1, bias=False), TcBatchNorm1d(3))
+        self.fuse_masking = nn.Sequential(TcConv1d(6, 2, 1, bias=False), TcBatchNorm1d(2))
 
     def forward(self, x, a_index=None, gumbels=None):
         """x (B,N,3), a_index (B,M) -> prob (B,M,9), masking (B,N,2) hard one-hot (straight-through)."""

@@ -16,13 +16,14 @@ import torch
 import torch.nn as nn
 
 from . import ops
+from .norm import ConvBlock, TcBatchNorm1d, TcBatchNorm2d
 from .tcconv import TcConv1d, TcConv2d
 
 _ACTS = {
     "relu": nn.ReLU, "leakyrelu": nn.LeakyReLU, "leaky_relu": nn.LeakyReLU, "gelu": nn.GELU,
     "silu": nn.SiLU, "swish": nn.SiLU, "sigmoid": nn.Sigmoid, "tanh": nn.Tanh, "elu": nn.ELU,
 }
-_NORMS = {"bn1d": nn.BatchNorm1d, "bn2d": nn.BatchNorm2d, "syncbn": nn.SyncBatchNorm,
+_NORMS = {"bn1d": TcBatchNorm1d, "bn2d": TcBatchNorm2d, "syncbn": nn.SyncBatchNorm,
           "in1d": nn.InstanceNorm1d, "in2d": nn.InstanceNorm2d}
 
 
@@ -82,7 +83,7 @@ def _block(make_linear, dim, cin, cout, norm_args, act_args, order, bias):
             mods.append(norm)
     else:
         raise NotImplementedError(f"{order} is not supported")
-    return nn.Sequential(*mods)
+    return ConvBlock(*mods)
 
 
 def create_convblock2d(cin, cout, norm_args=None, act_args=None, order="conv-norm-act", bias=True, **kw):

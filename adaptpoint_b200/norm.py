@@ -1,0 +1,225 @@
+"""Training-mode BatchNorm (+ReLU) and BatchNorm -> max-over-K on libapb200's streaming kernels (csrc/norm.cu).
+
+The reference builds every conv block as Conv -> BatchNorm{1,2}d -> ReLU (openpoints/models/layers/conv.py:24-103,
+norm.py:57-71) and max-pools the neighbour dimension with torch.max (pointnext.py:134); torch runs these as separate
+cuDNN / native kernels.  Here
+  * `TcBatchNorm1d/2d`  keep nn.BatchNorm{1,2}d's parameters, buffers and state_dict; in training mode on the "tc"
+    backend they run two fused passes forward and two backward (optionally with the following ReLU folded in);
+  * `bn_max(y, bn, relu)` computes max_k relu?(BN(y)) for y (B,C,M,K) in ONE read pass (batch statistics and the
+    per-(b,c,m) max/min/arg together; BN is monotone per channel so max_k BN(y) = BN(max_k y) or BN(min_k y)) and its
+    backward in one read + one write pass;
+  * `ConvBlock` is the nn.Sequential of a conv block that applies those fusions when it can.
+SyncBatchNorm semantics (the reference converts to SyncBN whenever world_size > 1, main.py:27): set
+`module.process_group` (see `enable_sync`) and the (C,2) statistics are all-reduced between the two passes.
+With the backend at "torch", or in eval mode, everything falls through to the stock torch modules.
+"""
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+import torch.nn.functional as F
+from torch.autograd import Function
+
+from . import _cabi
+from . import tcconv
+
+
+def _dims(x):
+    B, C = x.shape[0], x.shape[1]
+    P = 1
+    for d in x.shape[2:]:
+        P *= d
+    return B, C, P
+
+
+def _allreduce(t, group):
+    if group is not None and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(t, group=group)
+        return dist.get_world_size(group)
+    return 1
+
+
+class BatchNormActFn(Function):
+    """y = relu?(BN_batchstats(x)); x (B,C,*) f32 contiguous."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, running_mean, running_var, momentum, eps, relu, group):
+        xs = x.contiguous()
+        B, C, P = _dims(xs)
+        dev = xs.device
+        stats = torch.zeros((C, 2), dtype=torch.float64, device=dev)
+        _cabi.call("apb_bn_stats_f32", [xs, stats, B, C, P], dev)
+        world = _allreduce(stats, group)
+        count = float(B * P * world)
+        y = torch.empty_like(xs)
+        save_mean = torch.empty(C, dtype=torch.float32, device=dev)
+        save_rstd = torch.empty(C, dtype=torch.float32, device=dev)
+        _cabi.call("apb_bn_apply_f32", [xs, stats, weight, bias, float(eps), count, int(relu), y, save_mean, save_rstd,
+                                        running_mean, running_var, float(momentum), B, C, P], dev)
+        ctx.save_for_backward(xs, y if relu else None, weight, save_mean, save_rstd)
+        ctx.relu, ctx.group, ctx.count = relu, group, count
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        xs, y, weight, save_mean, save_rstd = ctx.saved_tensors
+        B, C, P = _dims(xs)
+        dev = xs.device
+        g = gy.contiguous().float()
+        stats2 = torch.zeros((C, 2), dtype=torch.float64, device=dev)
+        _cabi.call("apb_bn_bwd_reduce_f32", [xs, g, y, save_mean, save_rstd, stats2, B, C, P], dev)
+        local = stats2.clone() if ctx.group is not None else stats2
+        _allreduce(stats2, ctx.group)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(xs)
+            _cabi.call("apb_bn_bwd_apply_f32", [xs, g, y, save_mean, save_rstd, weight, stats2, ctx.count, dx, B, C, P],
+                       dev)
+        # parameter gradients are per-rank sums (the data-parallel all-reduce averages them afterwards)
+        return dx, local[:, 1].float(), local[:, 0].float(), None, None, None, None, None, None
+
+
+class BNMaxFn(Function):
+    """out (B,C,M) = max_k relu?(BN(y))  for y (B,C,M,K); `training` selects batch vs running statistics."""
+
+    @staticmethod
+    def forward(ctx, y, weight, bias, running_mean, running_var, momentum, eps, relu, training, group):
+        ys = y.contiguous()
+        B, C, M, K = ys.shape
+        dev = ys.device
+        vmax = torch.empty((B, C, M), dtype=torch.float32, device=dev)
+        vmin = torch.empty_like(vmax)
+        arg = torch.empty((B, C, M), dtype=torch.int32, device=dev)
+        stats = torch.zeros((C, 2), dtype=torch.float64, device=dev) if training else None
+        _cabi.call("apb_kmax_stats_f32", [ys, vmax, vmin, arg, stats, B, C, M, K], dev)
+        if training:
+            world = _allreduce(stats, group)
+            n = float(B * M * K * world)
+            mean_d = stats[:, 0] / n
+            var_d = (stats[:, 1] / n - mean_d * mean_d).clamp_min(0.0)
+            mean, rstd = mean_d.float(), torch.rsqrt(var_d + eps).float()
+            if running_mean is not None:
+                with torch.no_grad():
+                    running_mean.mul_(1 - momentum).add_(mean, alpha=momentum)
+                    running_var.mul_(1 - momentum).add_((var_d * (n / max(n - 1.0, 1.0))).float(), alpha=momentum)
+        else:
+            n = 1.0
+            mean, rstd = running_mean.float(), torch.rsqrt(running_var.float() + eps)
+        scale = weight * rstd
+        shift = bias - mean * scale
+        pos = (scale >= 0).view(1, C, 1)
+        sel = torch.where(pos, vmax, vmin)
+        arg_sel = torch.where(pos, arg & 0xFFFF, arg >> 16)
+        out = sel * scale.view(1, C, 1) + shift.view(1, C, 1)
+        if relu:
+            out = out.clamp_min_(0.0)
+        ctx.save_for_backward(ys, sel, arg_sel, out if relu else None, scale, mean, rstd)
+        ctx.cfg = (relu, training, group, n)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        ys, sel, arg_sel, out, scale, mean, rstd = ctx.saved_tensors
+        relu, training, group, n = ctx.cfg
+        B, C, M, K = ys.shape
+        dev = ys.device
+        g = g.contiguous().float()
+        if relu:
+            g = g * (out > 0)
+        sg = g.sum(dim=(0, 2))
+        sgx = (g * ((sel - mean.view(1, C, 1)) * rstd.view(1, C, 1))).sum(dim=(0, 2))
+        dgamma, dbeta = sgx, sg
+        dy = None
+        if ctx.needs_input_grad[0]:
+            gsel = (g * scale.view(1, C, 1)).contiguous()
+            a = bcoef = None
+            if training:
+                tot = torch.stack([sg, sgx])
+                if group is not None:
+                    tot = tot.clone()
+                    _allreduce(tot, group)
+                tsg, tsgx = tot[0], tot[1]
+                bcoef = (-scale * rstd * tsgx / n).contiguous()
+                a = (-scale * tsg / n - bcoef * mean).contiguous()
+            dy = torch.empty_like(ys)
+            _cabi.call("apb_bnmax_bwd_f32", [ys if training else None, gsel, arg_sel.contiguous(), a, bcoef, dy,
+                                             B, C, M, K], dev)
+        return dy, dgamma, dbeta, None, None, None, None, None, None, None
+
+
+def _tc_ok(bn, x):
+    return (tcconv.get_conv_backend() == "tc" and x.is_cuda and x.dtype == torch.float32 and bn.affine
+            and bn.track_running_stats and bn.momentum is not None)
+
+
+class _TcBatchNormMixin:
+    process_group = None  # set by enable_sync(): SyncBatchNorm semantics over that group
+
+    def forward_act(self, x, relu):
+        """BatchNorm (+ReLU when `relu`) -- fused kernels in training mode on the tc backend, torch otherwise."""
+        if self.training and _tc_ok(self, x):
+            y = BatchNormActFn.apply(x, self.weight, self.bias, self.running_mean, self.running_var, self.momentum,
+                                     self.eps, relu, self.process_group)
+            self.num_batches_tracked.add_(1)
+            return y
+        y = super().forward(x)
+        return F.relu(y, inplace=True) if relu else y
+
+    def forward(self, x):
+        return self.forward_act(x, False)
+
+
+class TcBatchNorm1d(_TcBatchNormMixin, nn.BatchNorm1d):
+    pass
+
+
+class TcBatchNorm2d(_TcBatchNormMixin, nn.BatchNorm2d):
+    pass
+
+
+def bn_max(y, bn, relu):
+    """max over the last dim of relu?(bn(y)), y (B,C,M,K); fused when `bn` is a Tc BatchNorm on the tc backend."""
+    if isinstance(bn, _TcBatchNormMixin) and _tc_ok(bn, y) and y.dim() == 4:
+        out = BNMaxFn.apply(y, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.momentum, bn.eps, relu,
+                            bn.training, bn.process_group)
+        if bn.training:
+            bn.num_batches_tracked.add_(1)
+        return out
+    z = bn(y)
+    if relu:
+        z = F.relu(z, inplace=True)
+    return torch.max(z, dim=-1, keepdim=False)[0]
+
+
+class ConvBlock(nn.Sequential):
+    """Conv -> [BatchNorm] -> [ReLU] block (same children / state_dict as the reference's nn.Sequential,
+    conv.py:24-103); folds the ReLU into the BatchNorm kernels when the norm is a Tc BatchNorm."""
+
+    def forward(self, x):
+        mods = list(self)
+        i = 0
+        while i < len(mods):
+            m = mods[i]
+            if (isinstance(m, _TcBatchNormMixin) and i + 1 < len(mods) and isinstance(mods[i + 1], nn.ReLU)):
+                x = m.forward_act(x, True)
+                i += 2
+                continue
+            x = m(x)
+            i += 1
+        return x
+
+    def split_for_pool(self):
+        """(conv, bn, relu?) when the block is exactly Conv -> TcBatchNorm [-> ReLU], else None."""
+        mods = list(self)
+        if len(mods) in (2, 3) and isinstance(mods[1], _TcBatchNormMixin) and \
+                (len(mods) == 2 or isinstance(mods[2], nn.ReLU)):
+            return mods[0], mods[1], len(mods) == 3
+        return None
+
+
+def enable_sync(module, group=None):
+    """SyncBatchNorm semantics for every Tc BatchNorm under `module` (statistics all-reduced over `group`)."""
+    group = group if group is not None else (dist.group.WORLD if dist.is_initialized() else None)
+    for m in module.modules():
+        if isinstance(m, _TcBatchNormMixin):
+            m.process_group = group
+    return module

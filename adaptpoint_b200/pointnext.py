@@ -19,6 +19,7 @@ import torch
 import torch.nn as nn
 
 from . import ops
+from .norm import ConvBlock, bn_max
 from .layers import (CHANNEL_MAP, create_act, create_convblock1d, create_convblock2d, create_grouper,
                      get_aggregation_feautres, QueryAndGroup)
 
@@ -52,7 +53,20 @@ def _aggregate(mod, query_p, p, f):
         from . import fused
         return fused.sa_fused_forward(mod, mod.grouper, mod.convs, query_p, p, f)
     dp, fj = mod.grouper(query_p, p, f)
-    return mod.pool(mod.convs(get_aggregation_feautres(query_p, dp, None, fj, "dp_fj")))
+    return _convs_pool(mod, get_aggregation_feautres(query_p, dp, None, fj, "dp_fj"))
+
+
+def _convs_pool(mod, x):
+    """pool(convs(x)); when the pool is max and the last block is Conv -> BatchNorm [-> ReLU], the BatchNorm,
+    activation and max over the neighbours run as norm.bn_max (one read pass, no normalised (B,C,M,K) tensor)."""
+    last = mod.convs[-1]
+    split = last.split_for_pool() if (isinstance(last, ConvBlock) and mod.reduction == "max") else None
+    if split is None:
+        return mod.pool(mod.convs(x))
+    for blk in list(mod.convs)[:-1]:
+        x = blk(x)
+    conv, bn, relu = split
+    return bn_max(conv(x), bn, relu)
 
 
 class LocalAggregation(nn.Module):
@@ -81,7 +95,7 @@ class LocalAggregation(nn.Module):
         if self.feature_type == "dp_fj":
             return _aggregate(self, p, p, f)
         dp, fj = self.grouper(p, p, f)
-        return self.pool(self.convs(get_aggregation_feautres(p, dp, f, fj, self.feature_type)))
+        return _convs_pool(self, get_aggregation_feautres(p, dp, f, fj, self.feature_type))
 
 
 class SetAbstraction(nn.Module):
@@ -131,7 +145,7 @@ class SetAbstraction(nn.Module):
             return p, self.convs(f)
         if self.all_aggr:
             dp, fj = self.grouper(p, p, f)
-            return p, self.pool(self.convs(get_aggregation_feautres(p, dp, None, fj, self.feature_type)))
+            return p, _convs_pool(self, get_aggregation_feautres(p, dp, None, fj, self.feature_type))
         idx = self.sample_fn(p, p.shape[1] // self.stride).long()
         new_p = torch.gather(p, 1, idx.unsqueeze(-1).expand(-1, -1, 3))
         fi = identity = None
@@ -143,7 +157,7 @@ class SetAbstraction(nn.Module):
             out = _aggregate(self, new_p, p, f)
         else:
             dp, fj = self.grouper(new_p, p, f)
-            out = self.pool(self.convs(get_aggregation_feautres(new_p, dp, fi, fj, self.feature_type)))
+            out = _convs_pool(self, get_aggregation_feautres(new_p, dp, fi, fj, self.feature_type))
         if self.use_res:
             out = self.act(out + identity)
         return new_p, out

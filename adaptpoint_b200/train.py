@@ -21,7 +21,7 @@ import torch
 import torch.distributed as dist
 import torch.nn as nn
 
-from . import ops, tcconv
+from . import norm, ops, tcconv
 from .imitator import AdaptPoint_Augmentor, PointDiscriminator1, PointWOLF_classversion
 from .models import SmoothCrossEntropy, build_model
 
@@ -87,8 +87,14 @@ class AdaptPointTrainer:
         self.generator = AdaptPoint_Augmentor(**self.cfg["adaptmodel_gan"]).to(self.device)
         self.discriminator = PointDiscriminator1(**self.cfg["adaptmodel_dis"]).to(self.device)
         if _world() > 1:
-            self.classifier = nn.SyncBatchNorm.convert_sync_batchnorm(self.classifier)
-            self.generator = nn.SyncBatchNorm.convert_sync_batchnorm(self.generator)
+            if self.device.type != "cuda":
+                pass                         # torch's SyncBatchNorm has no CPU path (gloo tests): per-rank statistics
+            elif self.conv_backend == "tc":    # our BatchNorm kernels all-reduce their (C,2) statistics themselves
+                norm.enable_sync(self.classifier)
+                norm.enable_sync(self.generator)
+            else:
+                self.classifier = nn.SyncBatchNorm.convert_sync_batchnorm(self.classifier)
+                self.generator = nn.SyncBatchNorm.convert_sync_batchnorm(self.generator)
             for net in (self.classifier, self.generator, self.discriminator):      # same init on every rank
                 for t in list(net.parameters()) + list(net.buffers()):
                     dist.broadcast(t.data, 0)

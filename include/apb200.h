@@ -142,6 +142,34 @@ int apb_sa_fused_fwd_bf16(const float *xyz, const float *new_xyz, const float *f
                           float *out, int B, int N, int M, int K, int Cin, int C1, int K1p, int C2, int K2p,
                           apb_stream_t stream);
 
+/* ---- BatchNorm (batch statistics) (+ReLU) and BatchNorm + max over K, channel-major (B,C,P) f32 -------------------
+ * No native counterpart in the reference: it runs nn.BatchNorm{1,2}d (openpoints/models/layers/norm.py:57-71) and
+ * torch.max over the neighbour dim (pointnext.py:134) through torch/cuDNN.  stats / stats2 are (C,2) fp64
+ * accumulators, zeroed by the caller (and all-reduced across ranks by the caller for SyncBatchNorm).
+ *   apb_bn_stats_f32       stats[c]  += (sum x, sum x^2)
+ *   apb_bn_apply_f32       y = act(gamma * (x - mean) * rstd + beta); writes save_mean/save_rstd (C); updates
+ *                          running_mean/var (may be NULL) with `momentum` and the unbiased variance; count = elements
+ *                          per channel over all ranks
+ *   apb_bn_bwd_reduce_f32  stats2[c] += (sum dy', sum dy' * xhat), dy' = dy * [y_relu > 0] if y_relu given
+ *   apb_bn_bwd_apply_f32   dx = gamma * rstd * (dy' - mean(dy') - xhat * mean(dy' xhat))
+ *   apb_kmax_stats_f32     y (B,C,M,K): vmax/vmin (B,C,M), arg = argmax | argmin << 16 (first index on ties),
+ *                          stats[c] += (sum, sum of squares) (stats may be NULL)
+ *   apb_bnmax_bwd_f32      dy[b,c,m,k] = gsel[b,c,m] * [k == arg[b,c,m]] + a[c] + bcoef[c] * y[b,c,m,k]
+ *                          (a / bcoef NULL = 0; y may be NULL when bcoef is) */
+int apb_bn_stats_f32(const float *x, double *stats, int B, int C, long long P, apb_stream_t stream);
+int apb_bn_apply_f32(const float *x, const double *stats, const float *gamma, const float *beta, float eps,
+                     double count, int relu, float *y, float *save_mean, float *save_rstd, float *running_mean,
+                     float *running_var, float momentum, int B, int C, long long P, apb_stream_t stream);
+int apb_bn_bwd_reduce_f32(const float *x, const float *dy, const float *y_relu, const float *save_mean,
+                          const float *save_rstd, double *stats2, int B, int C, long long P, apb_stream_t stream);
+int apb_bn_bwd_apply_f32(const float *x, const float *dy, const float *y_relu, const float *save_mean,
+                         const float *save_rstd, const float *gamma, const double *stats2, double count, float *dx,
+                         int B, int C, long long P, apb_stream_t stream);
+int apb_kmax_stats_f32(const float *y, float *vmax, float *vmin, int32_t *arg, double *stats, int B, int C, int M,
+                       int K, apb_stream_t stream);
+int apb_bnmax_bwd_f32(const float *y, const float *gsel, const int32_t *arg, const float *a, const float *bcoef,
+                      float *dy, int B, int C, int M, int K, apb_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

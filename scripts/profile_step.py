@@ -10,6 +10,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from bench import loader_batch, B_PER_GPU, N_POINTS  # noqa: E402
 from adaptpoint_b200.train import AdaptPointTrainer  # noqa: E402
+from adaptpoint_b200 import tcconv  # noqa: E402
 
 dev = torch.device("cuda:0")
 torch.backends.cudnn.allow_tf32 = False
@@ -20,6 +21,7 @@ pts, y = pts.to(dev), y.to(dev)
 for _ in range(3):
     tr.step(pts.clone(), y)
 torch.cuda.synchronize()
+tcconv.set_conv_backend(tr.conv_backend)   # the direct phase calls below bypass tr.step's context
 
 
 def timed(fn, n=5):
