@@ -33,6 +33,7 @@ _SIGNATURES = {
     "apb_pwconv_fwd_bf16": [_p, _p, _p, _p, _i, _p, _i, _i, _i, _i, _i, _p],
     "apb_pwconv_fwd_tf32": [_p, _p, _p, _p, _i, _p, _i, _i, _i, _i, _i, _p],
     "apb_pwconv_wgrad_tf32": [_p, _p, _p, _i, _i, _i, _i, _p],
+    "apb_affine_f32": [_p, _p, _p, _p, _i, _p, _i, _i, _ll, _p],
     "apb_bn_stats_f32": [_p, _p, _i, _i, _ll, _p],
     "apb_bn_apply_f32": [_p, _p, _p, _p, _f, _d, _i, _p, _p, _p, _p, _p, _f, _i, _i, _ll, _p],
     "apb_bn_bwd_reduce_f32": [_p, _p, _p, _p, _p, _p, _i, _i, _ll, _p],

@@ -282,6 +282,40 @@ __global__ void __launch_bounds__(NT) bnmax_bwd_kernel(const float *__restrict__
     }
 }
 
+// eval-mode BatchNorm (running statistics) is a per-channel affine map: y = act(scale[c] * x + shift[c]);
+// with dy given instead (bwd = 1): dx = scale[c] * dy * [y_relu > 0]
+__global__ void __launch_bounds__(NT) affine_kernel(const float *__restrict__ x, const float *__restrict__ y_relu,
+                                                    const float *__restrict__ scale, const float *__restrict__ shift,
+                                                    int relu, float *__restrict__ out, int C, long long P) {
+    const int c = blockIdx.y, b = blockIdx.z;
+    const size_t off = ((size_t)b * C + c) * P;
+    const float sc = scale[c], sh = shift ? shift[c] : 0.f;
+    const long long p0 = (long long)blockIdx.x * CHUNK;
+    const long long p1 = min(P, p0 + CHUNK);
+    const bool vec = (P & 3) == 0 && (((reinterpret_cast<uintptr_t>(x + off) | reinterpret_cast<uintptr_t>(out + off) |
+                                        (y_relu ? reinterpret_cast<uintptr_t>(y_relu + off) : 0)) & 15) == 0);
+    if (vec) {
+        for (long long i = p0 + threadIdx.x * 4; i < p1; i += NT * 4) {
+            float4 v = apb_ld_nc_f4(x + off + i);
+            v.x = fmaf(v.x, sc, sh); v.y = fmaf(v.y, sc, sh); v.z = fmaf(v.z, sc, sh); v.w = fmaf(v.w, sc, sh);
+            if (relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+            if (y_relu) {
+                const float4 m = apb_ld_nc_f4(y_relu + off + i);
+                v.x = m.x > 0.f ? v.x : 0.f; v.y = m.y > 0.f ? v.y : 0.f;
+                v.z = m.z > 0.f ? v.z : 0.f; v.w = m.w > 0.f ? v.w : 0.f;
+            }
+            *reinterpret_cast<float4 *>(out + off + i) = v;
+        }
+    } else {
+        for (long long i = p0 + threadIdx.x; i < p1; i += NT) {
+            float v = fmaf(__ldg(x + off + i), sc, sh);
+            if (relu) v = fmaxf(v, 0.f);
+            if (y_relu && !(__ldg(y_relu + off + i) > 0.f)) v = 0.f;
+            out[off + i] = v;
+        }
+    }
+}
+
 bool grid_ok(int B, int C) { return B <= 65535 && C <= 65535; }
 
 }  // namespace
@@ -361,6 +395,18 @@ extern "C" int apb_bnmax_bwd_f32(const float *y, const float *gsel, const int32_
     if (!grid_ok(B, C)) return APB_E_UNSUPPORTED;
     dim3 grid(apb_div_up(M, NT), C, B);
     bnmax_bwd_kernel<<<grid, NT, 0, (cudaStream_t)stream>>>(y, gsel, arg, a, bcoef, dy, C, M, K);
+    APB_CHECK_LAUNCH();
+    return APB_OK;
+}
+
+extern "C" int apb_affine_f32(const float *x, const float *mask_relu, const float *scale, const float *shift, int relu,
+                              float *out, int B, int C, long long P, apb_stream_t stream) {
+    if (B < 0 || C < 0 || P < 0) return APB_E_INVALID;
+    if (B == 0 || C == 0 || P == 0) return APB_OK;
+    if (!x || !scale || !out) return APB_E_INVALID;
+    if (!grid_ok(B, C)) return APB_E_UNSUPPORTED;
+    dim3 grid(apb_div_up(P, CHUNK), C, B);
+    affine_kernel<<<grid, NT, 0, (cudaStream_t)stream>>>(x, mask_relu, scale, shift, relu, out, C, P);
     APB_CHECK_LAUNCH();
     return APB_OK;
 }

@@ -78,6 +78,42 @@ class BatchNormActFn(Function):
         return dx, local[:, 1].float(), local[:, 0].float(), None, None, None, None, None, None
 
 
+class BatchNormEvalFn(Function):
+    """y = relu?(scale * x + shift) with the running statistics folded into (scale, shift); autograd-capable
+    (the AdaptPoint feedback loss back-propagates through the eval-mode classifier, ganloss_cls.py:44-49)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, running_mean, running_var, eps, relu):
+        xs = x.contiguous()
+        B, C, P = _dims(xs)
+        rstd = torch.rsqrt(running_var.float() + eps)
+        scale = (weight * rstd).contiguous()
+        shift = (bias - running_mean * scale).contiguous()
+        y = torch.empty_like(xs)
+        _cabi.call("apb_affine_f32", [xs, None, scale, shift, int(relu), y, B, C, P], xs.device)
+        need_param_grads = weight.requires_grad or bias.requires_grad
+        ctx.save_for_backward(xs if need_param_grads else None, y if relu else None, scale, running_mean, rstd)
+        ctx.relu = relu
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        xs, y, scale, mean, rstd = ctx.saved_tensors
+        g = gy.contiguous().float()
+        B, C, P = _dims(g)
+        dev = g.device
+        dx = dgamma = dbeta = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(g)
+            _cabi.call("apb_affine_f32", [g, y, scale, None, 0, dx, B, C, P], dev)
+        if (ctx.needs_input_grad[1] or ctx.needs_input_grad[2]) and xs is not None:
+            stats2 = torch.zeros((C, 2), dtype=torch.float64, device=dev)
+            _cabi.call("apb_bn_bwd_reduce_f32", [xs, g, y, mean.float().contiguous(), rstd.contiguous(), stats2,
+                                                 B, C, P], dev)
+            dgamma, dbeta = stats2[:, 1].float(), stats2[:, 0].float()
+        return dx, dgamma, dbeta, None, None, None, None
+
+
 class BNMaxFn(Function):
     """out (B,C,M) = max_k relu?(BN(y))  for y (B,C,M,K); `training` selects batch vs running statistics."""
 
@@ -161,6 +197,8 @@ class _TcBatchNormMixin:
                                      self.eps, relu, self.process_group)
             self.num_batches_tracked.add_(1)
             return y
+        if not self.training and _tc_ok(self, x):
+            return BatchNormEvalFn.apply(x, self.weight, self.bias, self.running_mean, self.running_var, self.eps, relu)
         y = super().forward(x)
         return F.relu(y, inplace=True) if relu else y
 

@@ -153,7 +153,16 @@ class AdaptPointTrainer:
         ratio = cfg.get("feedbackloss_ratio", 1)
         g_loss = g_loss_raw
         if ratio > 0:
-            g_loss = g_loss_raw + feedback_loss(C, self.criterion, data_real, data_fake, self._rho) * ratio
+            # The classifier only relays gradients to the imitator here: its own parameter gradients are thrown away by
+            # `model_pointcloud.zero_grad()` (train_autoaug.py:232) before they are ever used, so they are not computed.
+            cparams = [p for p in C.parameters() if p.requires_grad]
+            for p in cparams:
+                p.requires_grad_(False)
+            try:
+                g_loss = g_loss_raw + feedback_loss(C, self.criterion, data_real, data_fake, self._rho) * ratio
+            finally:
+                for p in cparams:
+                    p.requires_grad_(True)
         self.opt_g.zero_grad()
         g_loss.backward()
         allreduce_grads(list(G.parameters()))

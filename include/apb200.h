@@ -156,6 +156,10 @@ int apb_sa_fused_fwd_bf16(const float *xyz, const float *new_xyz, const float *f
  *                          stats[c] += (sum, sum of squares) (stats may be NULL)
  *   apb_bnmax_bwd_f32      dy[b,c,m,k] = gsel[b,c,m] * [k == arg[b,c,m]] + a[c] + bcoef[c] * y[b,c,m,k]
  *                          (a / bcoef NULL = 0; y may be NULL when bcoef is) */
+/* out = act(scale[c] * x + shift[c]) * [mask_relu > 0]: eval-mode BatchNorm (+ReLU) forward (mask NULL) and its
+ * data gradient (x := dy, shift NULL, relu 0, mask := the forward output when ReLU was applied). */
+int apb_affine_f32(const float *x, const float *mask_relu, const float *scale, const float *shift, int relu, float *out,
+                   int B, int C, long long P, apb_stream_t stream);
 int apb_bn_stats_f32(const float *x, double *stats, int B, int C, long long P, apb_stream_t stream);
 int apb_bn_apply_f32(const float *x, const double *stats, const float *gamma, const float *beta, float eps,
                      double count, int relu, float *y, float *save_mean, float *save_rstd, float *running_mean,

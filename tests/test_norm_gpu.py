@@ -89,9 +89,9 @@ def test_model_grads_tc_norm_vs_torch(cuda_dev):
     from adaptpoint_b200.synth import make_clouds
     torch.manual_seed(0)
     model = build_model("pointnext-s").to(cuda_dev).train()
-    xyz = make_clouds(8, 1024, "shell", 3).to(cuda_dev)
+    xyz = make_clouds(32, 1024, "shell", 3).to(cuda_dev)
     x = torch.cat([xyz, xyz[:, :, 1:2] - xyz[:, :, 1:2].amin(1, keepdim=True)], -1).transpose(1, 2).contiguous()
-    y = torch.arange(8, device=cuda_dev) % 15
+    y = torch.arange(32, device=cuda_dev) % 15
     state = copy.deepcopy(model.state_dict())
     outs = {}
     for mode in ("torch", "tcnorm"):
@@ -122,3 +122,32 @@ def test_model_grads_tc_norm_vs_torch(cuda_dev):
         assert cos > 0.99, (n, cos)
     for n, bref in outs["torch"][2].items():
         assert _rel(outs["tcnorm"][2][n].float(), bref.float()) < 2e-2, n
+
+
+@pytest.mark.parametrize("shape,relu,param_grads", [((4, 32, 512, 32), True, True), ((3, 67, 1001), False, True),
+                                                    ((2, 64, 128, 32), True, False)])
+def test_bn_eval_autograd(cuda_dev, shape, relu, param_grads):
+    """Eval-mode BatchNorm (+ReLU) under autograd (the feedback-loss path), with and without parameter gradients."""
+    from adaptpoint_b200 import tcconv
+    gen = torch.Generator().manual_seed(sum(shape))
+    bn = _mk_bn(shape[1], 2 if len(shape) == 4 else 1, gen, cuda_dev).eval()
+    ref = copy.deepcopy(bn)
+    for m in (bn, ref):
+        for p in m.parameters():
+            p.requires_grad_(param_grads)
+    x = torch.randn(shape, generator=gen).to(cuda_dev)
+    gy = torch.randn(shape, generator=gen).to(cuda_dev)
+    xr = x.clone().requires_grad_(True)
+    want = ref(xr)
+    if relu:
+        want = torch.relu(want)
+    want.backward(gy)
+    xt = x.clone().requires_grad_(True)
+    with tcconv.conv_backend("tc"):
+        got = bn.forward_act(xt, relu)
+        got.backward(gy)
+    assert _rel(got, want) < TOL and _rel(xt.grad, xr.grad) < TOL
+    if param_grads:
+        assert _rel(bn.weight.grad, ref.weight.grad) < TOL and _rel(bn.bias.grad, ref.bias.grad) < TOL
+    else:
+        assert bn.weight.grad is None
