@@ -19,6 +19,7 @@ _d, _ll = ctypes.c_double, ctypes.c_longlong
 # name -> argtypes (all return int status unless noted)
 _SIGNATURES = {
     "apb_fps_f32": [_p, _p, _p, _i, _i, _i, _p],
+    "apb_tune_group": [_i, _i],
     "apb_gather_f32": [_p, _p, _p, _i, _i, _i, _i, _p],
     "apb_gather_grad_f32": [_p, _p, _p, _i, _i, _i, _i, _p],
     "apb_ball_query_f32": [_p, _p, _p, _i, _i, _i, _f, _i, _p],
@@ -80,6 +81,13 @@ def load():
 
 def version():
     return load().apb_version().decode()
+
+
+def tune_group(channels_per_cta=0, threads=0):
+    """Benchmarks only: override the grouping/gather forward work split (0, 0 = automatic)."""
+    status = load().apb_tune_group(int(channels_per_cta), int(threads))
+    if status != 0:
+        raise ApbError(f"apb_tune_group({channels_per_cta}, {threads}) rejected")
 
 
 def fps_block_size(n):

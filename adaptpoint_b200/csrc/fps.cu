@@ -22,6 +22,7 @@
 #include <cstdlib>
 #include <cstdio>
 #include "apb_common.cuh"
+#include "tc_ptx.cuh"
 
 namespace cg = cooperative_groups;
 
@@ -43,19 +44,61 @@ __host__ __device__ constexpr int brev_small(int v, int D) {
     return D == 1 ? 0 : D == 2 ? v : D == 4 ? (((v & 1) << 1) | (v >> 1)) : (((v & 1) << 2) | (v & 2) | (v >> 2));
 }
 
-template <int NT, int D, int Q>
+// st.async: store to a (possibly remote) CTA's shared memory and count the bytes on that CTA's mbarrier.
+__device__ __forceinline__ void st_async_v4(uint32_t raddr, int a, int b, int c, int d, uint32_t rbar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1,%2,%3,%4}, [%5];" ::"r"(
+                     raddr),
+                 "r"(a), "r"(b), "r"(c), "r"(d), "r"(rbar)
+                 : "memory");
+}
+__device__ __forceinline__ void st_async_b32(uint32_t raddr, int a, uint32_t rbar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(raddr),
+                 "r"(a), "r"(rbar)
+                 : "memory");
+}
+// Wait for a phase of a local mbarrier whose bytes are delivered by st.async from any CTA of the cluster
+// (acquire at cluster scope).  A peer that died would otherwise hang the GPU: trap after ~2^26 polls.
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    for (uint32_t spin = 0; !done; ++spin) {
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t"
+            "}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (spin > (1u << 26)) __trap();
+    }
+}
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t laddr, int rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(laddr), "r"(rank));
+    return r;
+}
+
+// MULTI = false: one CTA per cloud, slots exchanged with STS + bar.sync.
+// MULTI = true : p.C CTAs of one cluster per cloud; every warp's winner is pushed into every CTA's slot
+//                table with st.async, which also counts bytes on that CTA's mbarrier, so a round needs no
+//                cluster-wide barrier: each CTA just waits until its own table is complete.
+template <int NT, int D, int Q, bool MULTI>
 __global__ void __launch_bounds__(NT, 1) fps_kernel(const FpsParams p) {
     constexpr int PPT = D * Q;
     constexpr int NW = NT / 32;
-    extern __shared__ float smem[];
+    constexpr int MAXIT = MULTI ? (8 * NW + 31) / 32 : 1;  // slot-table passes of one warp (C <= 8)
+    extern __shared__ __align__(16) float smem[];
+    __shared__ uint64_t bars[2];
     float *sx = smem, *sy = sx + PPT * NT, *sz = sy + PPT * NT;
-    int *slots = reinterpret_cast<int *>(sz + PPT * NT);  // [2 parity][5 fields][nslots]
 
-    const int C = p.C;
+    const int C = MULTI ? p.C : 1;
     const int nslots = C * NW;
+    int4 *slotA = reinterpret_cast<int4 *>(sz + PPT * NT);      // [2 parity][nslots] (value, rank', x, y)
+    int *slotB = reinterpret_cast<int *>(slotA + 2 * nslots);   // [2 parity][nslots] z
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     unsigned crank = 0;
-    if (C > 1) crank = cg::this_cluster().block_rank();
+    if (MULTI) crank = cg::this_cluster().block_rank();
     const int cloud = blockIdx.y;
     const int N = p.N, L = p.L, bs = 1 << L;
     const float *xyz = p.xyz + (size_t)cloud * N * 3;
@@ -100,70 +143,96 @@ __global__ void __launch_bounds__(NT, 1) fps_kernel(const FpsParams p) {
     }
     float cx = xyz[0], cy = xyz[1], cz = xyz[2];
     if (g == 0) out[0] = 0;
-    if (C > 1) cg::this_cluster().sync(); else __syncthreads();
+    if (MULTI) {
+        if (tid == 0) {
+            tc::mbar_init(&bars[0], 1);
+            tc::mbar_init(&bars[1], 1);
+            tc::fence_barrier_init();
+        }
+        cg::this_cluster().sync();
+    } else {
+        __syncthreads();
+    }
+    const uint32_t slotA_s = tc::smem_u32(slotA), slotB_s = tc::smem_u32(slotB);
+    const uint32_t bars_s = tc::smem_u32(bars);
+    const int si = crank * NW + warp;  // this warp's slot
 
     const unsigned qmask = (1u << p.QB) - 1u;
     for (int j = 1; j < p.m; ++j) {
-        float best = -1.f;
-        int bests = 0;
+        const int par = j & 1;
+        if (MULTI && tid == 0) tc::mbar_arrive_expect_tx(&bars[par], (uint32_t)nslots * 20u);
+        // per-thread arg-max, first (lowest rank') point wins ties: pairwise tree with "left wins"
+        float v[PPT];
+        int id[PPT];
 #pragma unroll
         for (int s = 0; s < PPT; ++s) {
             const float d = apb_sqdist(x[s] - cx, y[s] - cy, z[s] - cz);
-            const float d2 = fminf(d, md[s]);
-            md[s] = d2;
-            const bool gt = d2 > best;
-            bests = gt ? s : bests;
-            best = gt ? d2 : best;
+            md[s] = fminf(d, md[s]);
+            v[s] = md[s];
+            id[s] = s;
         }
+#pragma unroll
+        for (int w = 1; w < PPT; w *= 2) {
+#pragma unroll
+            for (int s = 0; s + w < PPT; s += 2 * w) {
+                const bool gt = v[s + w] > v[s];
+                id[s] = gt ? id[s + w] : id[s];
+                v[s] = gt ? v[s + w] : v[s];
+            }
+        }
+        const bool any = v[0] > -1.f;  // the reference starts from best = -1, besti = 0
+        const float best = any ? v[0] : -1.f;
+        const int bests = any ? id[0] : 0;
         const unsigned rank = ((rb + (unsigned)(bests / Q)) << p.QB) | (unsigned)(qbase + bests % Q);
         const int vbits = __float_as_int(best);
         const int wv = __reduce_max_sync(0xffffffffu, vbits);
-        const unsigned wr = __reduce_min_sync(0xffffffffu, vbits == wv ? rank : 0xffffffffu);
-        int *sl = slots + (j & 1) * 5 * nslots;
-        if (vbits == wv && rank == wr) {  // exactly one lane: rank' is unique per (thread, slot)
+        const unsigned cand = vbits == wv ? rank : 0xffffffffu;
+        const unsigned wr = __reduce_min_sync(0xffffffffu, cand);
+        if (cand == wr) {  // exactly one lane: rank' is unique per (thread, slot)
             const int wx = __float_as_int(sx[bests * NT + tid]);
             const int wy = __float_as_int(sy[bests * NT + tid]);
             const int wz = __float_as_int(sz[bests * NT + tid]);
-            const int si = crank * NW + warp;
-            if (C > 1) {
-                cg::cluster_group cl = cg::this_cluster();
+            if (MULTI) {
+                const uint32_t la = slotA_s + (uint32_t)(par * nslots + si) * 16u;
+                const uint32_t lb = slotB_s + (uint32_t)(par * nslots + si) * 4u;
+                const uint32_t lbar = bars_s + (uint32_t)par * 8u;
                 for (int c = 0; c < C; ++c) {
-                    int *r = cl.map_shared_rank(sl, c);
-                    r[si] = wv;
-                    r[nslots + si] = (int)wr;
-                    r[2 * nslots + si] = wx;
-                    r[3 * nslots + si] = wy;
-                    r[4 * nslots + si] = wz;
+                    const uint32_t rbar = map_to_cta(lbar, c);
+                    st_async_v4(map_to_cta(la, c), wv, (int)wr, wx, wy, rbar);
+                    st_async_b32(map_to_cta(lb, c), wz, rbar);
                 }
             } else {
-                sl[si] = wv;
-                sl[nslots + si] = (int)wr;
-                sl[2 * nslots + si] = wx;
-                sl[3 * nslots + si] = wy;
-                sl[4 * nslots + si] = wz;
+                slotA[par * nslots + si] = make_int4(wv, (int)wr, wx, wy);
+                slotB[par * nslots + si] = wz;
             }
         }
-        if (C > 1) cg::this_cluster().sync(); else __syncthreads();
+        // bars[par] is used in rounds par, par+2, ...: its ((j-1)/2)-th phase
+        if (MULTI) mbar_wait_cluster(bars_s + (uint32_t)par * 8u, (uint32_t)((j - 1) >> 1) & 1u); else __syncthreads();
 
-        int bv = INT_MIN;
+        // every warp reduces the slot table redundantly
+        int bv = INT_MIN, bx = 0, by = 0, bz = 0;
         unsigned br = 0xffffffffu;
-        int bi = -1;
-        for (int i = lane; i < nslots; i += 32) {
-            const int v = sl[i];
-            const unsigned r = (unsigned)sl[nslots + i];
-            const bool better = v > bv || (v == bv && r < br);
-            bv = better ? v : bv;
-            br = better ? r : br;
-            bi = better ? i : bi;
+#pragma unroll
+        for (int it = 0; it < MAXIT; ++it) {
+            const int i = lane + 32 * it;
+            if (i < nslots) {
+                const int4 a = slotA[par * nslots + i];
+                const int zz = slotB[par * nslots + i];
+                const bool better = a.x > bv || (a.x == bv && (unsigned)a.y < br);
+                bv = better ? a.x : bv;
+                br = better ? (unsigned)a.y : br;
+                bx = better ? a.z : bx;
+                by = better ? a.w : by;
+                bz = better ? zz : bz;
+            }
         }
         const int gv = __reduce_max_sync(0xffffffffu, bv);
-        const unsigned gr = __reduce_min_sync(0xffffffffu, bv == gv ? br : 0xffffffffu);
-        const unsigned ball = __ballot_sync(0xffffffffu, bv == gv && br == gr && bi >= 0);
-        const int src = __ffs(ball) - 1;
-        const int wi = __shfl_sync(0xffffffffu, bi, src);
-        cx = __int_as_float(sl[2 * nslots + wi]);
-        cy = __int_as_float(sl[3 * nslots + wi]);
-        cz = __int_as_float(sl[4 * nslots + wi]);
+        const unsigned gcand = bv == gv ? br : 0xffffffffu;
+        const unsigned gr = __reduce_min_sync(0xffffffffu, gcand);
+        const bool win = gcand == gr && gr != 0xffffffffu;  // one lane (rank' unique over the cloud)
+        cx = __int_as_float((int)__reduce_or_sync(0xffffffffu, win ? (unsigned)bx : 0u));
+        cy = __int_as_float((int)__reduce_or_sync(0xffffffffu, win ? (unsigned)by : 0u));
+        cz = __int_as_float((int)__reduce_or_sync(0xffffffffu, win ? (unsigned)bz : 0u));
         if (g == 0) {
             const unsigned hi = gr >> p.QB;
             const int t = L ? (int)(__brev(hi) >> (32 - L)) : 0;
@@ -180,14 +249,16 @@ __global__ void __launch_bounds__(NT, 1) fps_kernel(const FpsParams p) {
                 if (k < N) temp[k] = md[lp * Q + sq];
             }
     }
+    if (MULTI) cg::this_cluster().sync();  // no CTA leaves while a peer may still be storing into it
 }
 
 typedef void (*fps_fn_t)(const FpsParams);
 struct FpsVariant {
     int NT, D, Q;
-    fps_fn_t fn;
+    fps_fn_t fn;        // one CTA per cloud
+    fps_fn_t fn_multi;  // one cluster per cloud (NT >= 256 only)
 };
-#define V(NT, D, Q) {NT, D, Q, fps_kernel<NT, D, Q>}
+#define V(NT, D, Q) {NT, D, Q, fps_kernel<NT, D, Q, false>, (NT) >= 256 ? fps_kernel<(NT) >= 256 ? NT : 256, D, Q, true> : nullptr}
 const FpsVariant kVariants[] = {
     V(32, 1, 2),   V(64, 1, 2),   V(128, 1, 2),
     V(256, 1, 2),  V(256, 2, 2),  V(256, 4, 1),  V(256, 4, 2),  V(256, 4, 3),  V(256, 4, 4),
@@ -301,7 +372,9 @@ extern "C" int apb_fps_f32(const float *xyz, float *temp, int32_t *idx, int B, i
 
     const int NT = best.v->NT, PPT = best.v->D * best.v->Q, C = best.C;
     const size_t smem = (size_t)3 * PPT * NT * sizeof(float) + (size_t)2 * 5 * C * (NT / 32) * sizeof(int);
-    APB_CUDA(cudaFuncSetAttribute((const void *)best.v->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const fps_fn_t fn = C > 1 ? best.v->fn_multi : best.v->fn;
+    if (!fn) return APB_E_UNSUPPORTED;
+    APB_CUDA(cudaFuncSetAttribute((const void *)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
 
     FpsParams p{xyz, temp, idx, N, m, ilog2(bs), best.logT, best.QB, C};
     cudaLaunchConfig_t cfg{};
@@ -316,6 +389,6 @@ extern "C" int apb_fps_f32(const float *xyz, float *temp, int32_t *idx, int B, i
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    APB_CUDA(cudaLaunchKernelEx(&cfg, best.v->fn, p));
+    APB_CUDA(cudaLaunchKernelEx(&cfg, fn, p));
     return APB_OK;
 }

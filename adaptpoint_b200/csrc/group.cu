@@ -11,33 +11,56 @@
 // shared memory (bank-conflict bound, no sector waste) and emits float4 streaming stores, so HBM
 // sees the algorithmic bytes: C*N + M*K reads (idx re-reads hit L2) + C*M*K writes.
 #include "apb_common.cuh"
+#include "tc_ptx.cuh"
 
 namespace {
 
-constexpr int GT = 256;  // threads per CTA
+constexpr int GT = 256;  // threads per CTA (backward / interpolation kernels)
+
+// One-dimensional TMA bulk copy global -> shared, completion signalled on an mbarrier.
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     tc::smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(tc::smem_u32(bar))
+                 : "memory");
+}
 
 // out[b,c,p] = points[b,c,idx[b,p]]   p in [0,P) (P = M*K for grouping, m for gather)
 // grid: (position chunks, channel groups, B); dynamic smem: CH*N floats.
-template <int CH>
-__global__ void __launch_bounds__(GT) group_rows_kernel(const float *__restrict__ points,
+// The CH rows are contiguous in HBM: when 16-byte aligned they arrive as TMA bulk copies (<= 32 KB
+// pieces issued by the lanes of warp 0, one mbarrier), so the whole row set is in flight at once and
+// no register or LSU slot is spent on staging; the gather loop keeps two idx quads in flight.
+template <int CH, int NT>
+__global__ void __launch_bounds__(NT) group_rows_kernel(const float *__restrict__ points,
                                                          const int32_t *__restrict__ idx,
                                                          float *__restrict__ out, int C, int N, long long P,
                                                          int chunk) {
-    extern __shared__ float rows[];  // [CH][N]
+    extern __shared__ __align__(128) float rows[];  // [CH][N]
+    __shared__ uint64_t bar;
     const int b = blockIdx.z;
     const int c0 = blockIdx.y * CH;
     const int nch = min(CH, C - c0);
     const float *src = points + ((size_t)b * C + c0) * N;  // nch consecutive rows are contiguous
     const size_t total = (size_t)nch * N;
-    if (((reinterpret_cast<uintptr_t>(src) & 15) == 0)) {
-        const size_t nv = total >> 2;
-        for (size_t i = threadIdx.x; i < nv; i += GT)
-            reinterpret_cast<float4 *>(rows)[i] = __ldg(reinterpret_cast<const float4 *>(src) + i);
-        for (size_t i = (nv << 2) + threadIdx.x; i < total; i += GT) rows[i] = __ldg(src + i);
+    const size_t bytes = total * sizeof(float);
+    if (((reinterpret_cast<uintptr_t>(src) & 15) == 0) && ((bytes & 15) == 0)) {
+        constexpr uint32_t PIECE = 32768;
+        if (threadIdx.x == 0) {
+            tc::mbar_init(&bar, 1);
+            tc::fence_barrier_init();
+            tc::mbar_arrive_expect_tx(&bar, (uint32_t)bytes);
+        }
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            for (size_t off = (size_t)threadIdx.x * PIECE; off < bytes; off += (size_t)32 * PIECE)
+                bulk_g2s(reinterpret_cast<char *>(rows) + off, reinterpret_cast<const char *>(src) + off,
+                         (uint32_t)min((size_t)PIECE, bytes - off), &bar);
+        }
+        tc::mbar_wait(&bar, 0);
     } else {
-        for (size_t i = threadIdx.x; i < total; i += GT) rows[i] = __ldg(src + i);
+        for (size_t i = threadIdx.x; i < total; i += NT) rows[i] = __ldg(src + i);
+        __syncthreads();
     }
-    __syncthreads();
 
     const int32_t *ix = idx + (size_t)b * P;
     float *o = out + ((size_t)b * C + c0) * P;
@@ -46,8 +69,12 @@ __global__ void __launch_bounds__(GT) group_rows_kernel(const float *__restrict_
     const bool vec_ok = ((P & 3) == 0) && ((reinterpret_cast<uintptr_t>(ix) & 15) == 0) &&
                         ((reinterpret_cast<uintptr_t>(o) & 15) == 0);
     if (vec_ok) {  // chunk is a multiple of 4
-        for (long long p = p_begin + (long long)threadIdx.x * 4; p < p_end; p += GT * 4) {
-            const int4 i4 = apb_ld_nc_i4(ix + p);
+        long long p = p_begin + (long long)threadIdx.x * 4;
+        int4 nxt = make_int4(0, 0, 0, 0);
+        if (p < p_end) nxt = apb_ld_nc_i4(ix + p);
+        for (; p < p_end; p += NT * 4) {
+            const int4 i4 = nxt;
+            if (p + NT * 4 < p_end) nxt = apb_ld_nc_i4(ix + p + NT * 4);
 #pragma unroll
             for (int ch = 0; ch < CH; ++ch) {
                 if (ch < nch) {
@@ -59,7 +86,7 @@ __global__ void __launch_bounds__(GT) group_rows_kernel(const float *__restrict_
             }
         }
     } else {
-        for (long long p = p_begin + threadIdx.x; p < p_end; p += GT) {
+        for (long long p = p_begin + threadIdx.x; p < p_end; p += NT) {
             const int i = __ldg(ix + p);
 #pragma unroll
             for (int ch = 0; ch < CH; ++ch)
@@ -197,22 +224,33 @@ __global__ void __launch_bounds__(GT) three_interp_grad_kernel(const float *__re
 
 constexpr size_t kSmemBudget = 200 * 1024;
 
-template <int CH>
+// Benchmark-only override of the forward work split (apb_tune_group): 0 = automatic.
+int g_tune_ch = 0, g_tune_nt = 0;
+
+template <int CH, int NT>
 int launch_group_rows(const float *points, const int32_t *idx, float *out, int B, int C, int N, long long P,
                       cudaStream_t st) {
     const size_t smem = (size_t)CH * N * sizeof(float);
-    APB_CUDA(cudaFuncSetAttribute((const void *)group_rows_kernel<CH>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)smem));
+    APB_CUDA(cudaFuncSetAttribute((const void *)group_rows_kernel<CH, NT>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     // positions per CTA: enough output per staged row (>= 8x the row bytes) but keep the grid wide
     long long chunk = (long long)8 * N;
     if (chunk < 4096) chunk = 4096;
     const int cgroups = apb_div_up(C, CH);
     while (chunk > 4096 && (long long)apb_div_up(P, chunk) * cgroups * B < 4 * APB_NUM_SMS) chunk >>= 1;
-    chunk = (chunk + 1023) / 1024 * 1024;  // multiple of GT*4
+    chunk = (chunk + 4095) / 4096 * 4096;  // multiple of NT*4 for every NT
     dim3 grid(apb_div_up(P, chunk), cgroups, B);
-    group_rows_kernel<CH><<<grid, GT, smem, st>>>(points, idx, out, C, N, P, (int)chunk);
+    group_rows_kernel<CH, NT><<<grid, NT, smem, st>>>(points, idx, out, C, N, P, (int)chunk);
     APB_CHECK_LAUNCH();
     return APB_OK;
+}
+
+template <int CH>
+int launch_group_rows_nt(int nt, const float *points, const int32_t *idx, float *out, int B, int C, int N,
+                         long long P, cudaStream_t st) {
+    if (nt >= 1024) return launch_group_rows<CH, 1024>(points, idx, out, B, C, N, P, st);
+    if (nt >= 512) return launch_group_rows<CH, 512>(points, idx, out, B, C, N, P, st);
+    return launch_group_rows<CH, 256>(points, idx, out, B, C, N, P, st);
 }
 
 int group_forward(const float *points, const int32_t *idx, float *out, int B, int C, int N, long long P,
@@ -227,10 +265,31 @@ int group_forward(const float *points, const int32_t *idx, float *out, int B, in
         APB_CHECK_LAUNCH();
         return APB_OK;
     }
+    // Work split (fitted on B200, profiles/ops_group_tune_r01.jsonl).  Expanding calls (grouping, P >> N) are
+    // store-bound: stage as many channels per idx read as fit and give the CTA enough warps to cover the
+    // idx latency (1024 threads once the row set owns more than a quarter of the SM's shared memory).
+    // Load-bound calls (gather, P <= 2N) instead want several small CTAs per SM so one CTA's row copy
+    // overlaps another's gathers.
     const int fit = (int)(kSmemBudget / row);
-    if (fit >= 4 && C >= 4) return launch_group_rows<4>(points, idx, out, B, C, N, P, st);
-    if (fit >= 2 && C >= 2) return launch_group_rows<2>(points, idx, out, B, C, N, P, st);
-    return launch_group_rows<1>(points, idx, out, B, C, N, P, st);
+    int ch = 1, nt = 256;
+    if (P > 2LL * N) {
+        if (C >= 4 && fit >= 4) ch = 4;
+        else if (C >= 4 && fit >= 2) ch = 2;
+        const size_t smem = ch * row;
+        nt = smem > 50 * 1024 ? 1024 : (smem > 25 * 1024 ? 512 : 256);
+        if (ch == 1 && smem > 16 * 1024) nt = smem > 100 * 1024 ? 1024 : 512;
+    } else {
+        constexpr size_t kThird = 64 * 1024;
+        if (C >= 4 && 4 * row <= kThird) ch = 4;
+        else if (C >= 2 && 2 * row <= kThird) ch = 2;
+        nt = ch * row > 16 * 1024 ? 512 : 256;
+        if (row > 100 * 1024) nt = 1024;
+    }
+    if (g_tune_ch > 0 && g_tune_ch <= fit && g_tune_ch <= C) ch = g_tune_ch;
+    if (g_tune_nt > 0) nt = g_tune_nt;
+    if (ch >= 4) return launch_group_rows_nt<4>(nt, points, idx, out, B, C, N, P, st);
+    if (ch >= 2) return launch_group_rows_nt<2>(nt, points, idx, out, B, C, N, P, st);
+    return launch_group_rows_nt<1>(nt, points, idx, out, B, C, N, P, st);
 }
 
 int group_backward(const float *grad_out, const int32_t *idx, float *grad_points, int B, int C, int N,
@@ -246,6 +305,14 @@ int group_backward(const float *grad_out, const int32_t *idx, float *grad_points
 
 }  // namespace
 
+extern "C" int apb_tune_group(int channels_per_cta, int threads) {
+    if (channels_per_cta != 0 && channels_per_cta != 1 && channels_per_cta != 2 && channels_per_cta != 4)
+        return APB_E_INVALID;
+    if (threads != 0 && threads != 256 && threads != 512 && threads != 1024) return APB_E_INVALID;
+    g_tune_ch = channels_per_cta;
+    g_tune_nt = threads;
+    return APB_OK;
+}
 extern "C" int apb_group_f32(const float *points, const int32_t *idx, float *out, int B, int C, int N, int M,
                              int K, apb_stream_t stream) {
     if (B < 0 || C < 0 || N < 0 || M < 0 || K < 0) return APB_E_INVALID;

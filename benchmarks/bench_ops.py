@@ -47,6 +47,7 @@ def main():
     ap.add_argument("--no-ref", action="store_true")
     ap.add_argument("--ops", default="fps,ball_query,group,group_grad,gather")
     ap.add_argument("--out", default="")
+    ap.add_argument("--tune", action="store_true", help="also sweep the grouping work split (apb_tune_group)")
     args = ap.parse_args()
     dev = torch.device("cuda:0")
     hbm, src = peaks()
@@ -57,6 +58,9 @@ def main():
     flush = torch.zeros(160 * 1024 * 1024 // 4, device=dev)  # > 126 MB L2
     B = args.B
     lines = []
+    if args.out:
+        os.makedirs(os.path.dirname(args.out) or ".", exist_ok=True)
+        open(args.out, "w").close()
     for N in [int(s) for s in args.sizes.split(",")]:
         M, K = N // 4, 32
         xyz = make_clouds(B, N, "shell", seed=0).to(dev)
@@ -75,6 +79,9 @@ def main():
                 d.update(extra)
             lines.append(d)
             print(json.dumps(d), flush=True)
+            if args.out:  # append as we go: a later crash keeps what was measured
+                with open(args.out, "a") as f:
+                    f.write(json.dumps(d) + "\n")
 
         if "fps" in want:
             ms, mn = timeit(lambda: ops.furthest_point_sample(xyz, M), args.iters, flush=flush)
@@ -93,10 +100,24 @@ def main():
             if C * B * M * K * 4 > 24e9:
                 continue
             feat = torch.randn(B, C, N, device=dev)
+            # the reference kernels index with 32-bit ints (group_points_gpu.cu:62-71): skip them past 2^31 elements
+            ref_ok = refcuda is not None and B * C * M * K < 2 ** 31
+            if "group" in want and args.tune:
+                from adaptpoint_b200 import _cabi
+                for ch, nt in ((1, 256), (1, 512), (1, 1024), (2, 512), (2, 1024), (4, 256), (4, 512), (4, 1024)):
+                    if ch > C or ch * N * 4 > 200 * 1024:
+                        continue
+                    _cabi.tune_group(ch, nt)
+                    ms, mn = timeit(lambda: ops.grouping_operation(feat, nbr), args.iters, flush=flush)
+                    emit(f"group_C{C}@ch{ch}nt{nt}", ms, mn, 4.0 * B * (C * N + M * K + C * M * K), None)
+                    if C in (3, 128):
+                        ms, mn = timeit(lambda: ops.gather_operation(feat, idx), args.iters, flush=flush)
+                        emit(f"gather_C{C}@ch{ch}nt{nt}", ms, mn, 4.0 * B * (2 * C * M + M), None)
+                _cabi.tune_group(0, 0)
             if "group" in want:
                 ms, mn = timeit(lambda: ops.grouping_operation(feat, nbr), args.iters, flush=flush)
                 rms = None
-                if refcuda is not None:
+                if ref_ok:
                     rms, _ = timeit(lambda: refcuda.group(feat, nbr), max(2, args.iters // 2), warm=1)
                 emit(f"group_C{C}", ms, mn, 4.0 * B * (C * N + M * K + C * M * K), rms)
             if "group_grad" in want:
@@ -109,7 +130,7 @@ def main():
                     _cabi.call("apb_group_grad_f32", [go, nbr, gp, B, C, N, M, K], dev)
                 ms, mn = timeit(bwd, args.iters, flush=flush)
                 rms = None
-                if refcuda is not None:
+                if ref_ok:
                     rms, _ = timeit(lambda: refcuda.group_grad(go, nbr, N), max(2, args.iters // 2), warm=1)
                 emit(f"group_grad_C{C}", ms, mn, 4.0 * B * (C * M * K + M * K + C * N), rms)
                 del go, gp
@@ -120,11 +141,6 @@ def main():
                     rms, _ = timeit(lambda: refcuda.gather(feat, idx), max(2, args.iters // 2), warm=1)
                 emit(f"gather_C{C}", ms, mn, 4.0 * B * (2 * C * M + M), rms)
             del feat
-    if args.out:
-        os.makedirs(os.path.dirname(args.out), exist_ok=True)
-        with open(args.out, "w") as f:
-            for d in lines:
-                f.write(json.dumps(d) + "\n")
 
 
 if __name__ == "__main__":

@@ -50,6 +50,10 @@ int apb_fps_block_size(int n);
  * bit-reversed (k mod block_size), then smallest k). */
 int apb_fps_f32(const float *xyz, float *temp, int32_t *idx, int B, int N, int m, apb_stream_t stream);
 
+/* Benchmarks only: override the forward grouping/gather work split (channels staged per CTA in
+ * {0,1,2,4}, threads per CTA in {0,256,512,1024}; 0 = automatic).  No reference counterpart. */
+int apb_tune_group(int channels_per_cta, int threads);
+
 /* gather_points_wrapper(b,c,n,npoints,points,idx,out)      -- sampling.cpp:11-22 */
 int apb_gather_f32(const float *points, const int32_t *idx, float *out, int B, int C, int N, int m,
                    apb_stream_t stream);

@@ -32,6 +32,10 @@ elif tgt == "pw":
         fused.pwconv_forward(blk, x)
 elif tgt in ("fps", "group", "group_grad"):
     B, N, M, K, C = 32, 16384, 4096, 32, 32
+    if len(sys.argv) > 3:  # python scripts/ncu_targets.py fps 2048 1024 [C]
+        N, M = int(sys.argv[2]), int(sys.argv[3])
+    if len(sys.argv) > 4:
+        C = int(sys.argv[4])
     xyz = make_clouds(B, N, "shell", 0).to(dev)
     for _ in range(2):
         idx = ops.furthest_point_sample(xyz, M)
