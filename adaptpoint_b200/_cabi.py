@@ -25,6 +25,7 @@ _SIGNATURES = {
     "apb_ball_query_f32": [_p, _p, _p, _i, _i, _i, _f, _i, _p],
     "apb_knn_f32": [_p, _p, _p, _p, _i, _i, _i, _i, _p],
     "apb_group_f32": [_p, _p, _p, _i, _i, _i, _i, _i, _p],
+    "apb_group_minmax_f32": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p],
     "apb_group_grad_f32": [_p, _p, _p, _i, _i, _i, _i, _i, _p],
     "apb_three_nn_f32": [_p, _p, _p, _p, _i, _i, _i, _p],
     "apb_three_interp_f32": [_p, _p, _p, _p, _i, _i, _i, _i, _p],
@@ -40,6 +41,7 @@ _SIGNATURES = {
     "apb_bn_bwd_reduce_f32": [_p, _p, _p, _p, _p, _p, _i, _i, _ll, _p],
     "apb_bn_bwd_apply_f32": [_p, _p, _p, _p, _p, _p, _p, _d, _p, _i, _i, _ll, _p],
     "apb_kmax_stats_f32": [_p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
+    "apb_rowmax_f32": [_p, _p, _p, _ll, _i, _p],
     "apb_bnmax_bwd_f32": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
     "apb_sa_fused_fwd_bf16": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _i, _p, _p,
                               _i, _i, _i, _i, _i, _i, _i, _i, _i, _p],

@@ -292,6 +292,98 @@ int group_forward(const float *points, const int32_t *idx, float *out, int B, in
     return launch_group_rows_nt<1>(nt, points, idx, out, B, C, N, P, st);
 }
 
+// Grouping fused with the max / min over the K neighbours of each query:
+//   vmax[b,c,j] = max_k points[b,c,idx[b,j,k]]  (amax[b,c,j] = the POINT index attaining it, first k on ties), same for min.
+// This is what "group -> affine normalise -> max over neighbours" (generator_component4_15.py:368-431, PointsetGrouper) and
+// "group -> max" (Producefactor, :560-563) need: alpha*(g - centre) + beta is monotone in g, so the max over k of the
+// normalised tensor is the normalised max (alpha >= 0) or min (alpha < 0), bit for bit, and the (B,C,M,K) tensor, its
+// four elementwise passes and their backward passes disappear; the backward is a scatter of (B,C,M) values.
+template <int CH, int NT>
+__global__ void __launch_bounds__(NT) group_minmax_kernel(const float *__restrict__ points,
+                                                           const int32_t *__restrict__ idx, float *__restrict__ vmax,
+                                                           float *__restrict__ vmin, int32_t *__restrict__ amax,
+                                                           int32_t *__restrict__ amin, int C, int N, int M, int K,
+                                                           int mchunk) {
+    extern __shared__ __align__(128) float rows[];  // [CH][N]
+    __shared__ uint64_t bar;
+    const int b = blockIdx.z;
+    const int c0 = blockIdx.y * CH;
+    const int nch = min(CH, C - c0);
+    const float *src = points + ((size_t)b * C + c0) * N;
+    const size_t total = (size_t)nch * N;
+    const size_t bytes = total * sizeof(float);
+    if (((reinterpret_cast<uintptr_t>(src) & 15) == 0) && ((bytes & 15) == 0)) {
+        constexpr uint32_t PIECE = 32768;
+        if (threadIdx.x == 0) {
+            tc::mbar_init(&bar, 1);
+            tc::fence_barrier_init();
+            tc::mbar_arrive_expect_tx(&bar, (uint32_t)bytes);
+        }
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            for (size_t off = (size_t)threadIdx.x * PIECE; off < bytes; off += (size_t)32 * PIECE)
+                bulk_g2s(reinterpret_cast<char *>(rows) + off, reinterpret_cast<const char *>(src) + off,
+                         (uint32_t)min((size_t)PIECE, bytes - off), &bar);
+        }
+        tc::mbar_wait(&bar, 0);
+    } else {
+        for (size_t i = threadIdx.x; i < total; i += NT) rows[i] = __ldg(src + i);
+        __syncthreads();
+    }
+    const int j_end = min(M, (int)(blockIdx.x + 1) * mchunk);
+    const bool vec = (K & 3) == 0 && ((reinterpret_cast<uintptr_t>(idx) & 15) == 0);
+    for (int j = blockIdx.x * mchunk + threadIdx.x; j < j_end; j += NT) {
+        const int32_t *ix = idx + ((size_t)b * M + j) * K;
+        float mx[CH], mn[CH];
+        int ax[CH], an[CH];
+#pragma unroll
+        for (int ch = 0; ch < CH; ++ch) {
+            mx[ch] = -INFINITY; mn[ch] = INFINITY; ax[ch] = 0; an[ch] = 0;
+        }
+        auto upd = [&](int i) {
+#pragma unroll
+            for (int ch = 0; ch < CH; ++ch) {
+                if (ch < nch) {
+                    const float v = rows[(size_t)ch * N + i];
+                    if (v > mx[ch]) { mx[ch] = v; ax[ch] = i; }
+                    if (v < mn[ch]) { mn[ch] = v; an[ch] = i; }
+                }
+            }
+        };
+        if (vec) {
+            for (int k = 0; k < K; k += 4) {
+                const int4 i4 = *reinterpret_cast<const int4 *>(ix + k);
+                upd(i4.x); upd(i4.y); upd(i4.z); upd(i4.w);
+            }
+        } else {
+            for (int k = 0; k < K; ++k) upd(__ldg(ix + k));
+        }
+#pragma unroll
+        for (int ch = 0; ch < CH; ++ch) {
+            if (ch < nch) {
+                const size_t o = ((size_t)b * C + c0 + ch) * M + j;
+                vmax[o] = mx[ch]; vmin[o] = mn[ch]; amax[o] = ax[ch]; amin[o] = an[ch];
+            }
+        }
+    }
+}
+
+template <int CH>
+int launch_group_minmax(const float *points, const int32_t *idx, float *vmax, float *vmin, int32_t *amax,
+                        int32_t *amin, int B, int C, int N, int M, int K, cudaStream_t st) {
+    constexpr int NT = 256;
+    const size_t smem = (size_t)CH * N * sizeof(float);
+    APB_CUDA(cudaFuncSetAttribute((const void *)group_minmax_kernel<CH, NT>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int cgroups = apb_div_up(C, CH);
+    int mchunk = M;
+    while (mchunk > 2 * NT && (long long)apb_div_up(M, mchunk) * cgroups * B < 2 * APB_NUM_SMS) mchunk = (mchunk + 1) / 2;
+    dim3 grid(apb_div_up(M, mchunk), cgroups, B);
+    group_minmax_kernel<CH, NT><<<grid, NT, smem, st>>>(points, idx, vmax, vmin, amax, amin, C, N, M, K, mchunk);
+    APB_CHECK_LAUNCH();
+    return APB_OK;
+}
+
 int group_backward(const float *grad_out, const int32_t *idx, float *grad_points, int B, int C, int N,
                    long long P, cudaStream_t st) {
     if (B == 0 || C == 0 || P == 0) return APB_OK;
@@ -317,6 +409,20 @@ extern "C" int apb_group_f32(const float *points, const int32_t *idx, float *out
                              int K, apb_stream_t stream) {
     if (B < 0 || C < 0 || N < 0 || M < 0 || K < 0) return APB_E_INVALID;
     return group_forward(points, idx, out, B, C, N, (long long)M * K, (cudaStream_t)stream);
+}
+extern "C" int apb_group_minmax_f32(const float *points, const int32_t *idx, float *vmax, float *vmin, int32_t *amax,
+                                    int32_t *amin, int B, int C, int N, int M, int K, apb_stream_t stream) {
+    if (B < 0 || C < 0 || N < 0 || M < 0 || K < 0) return APB_E_INVALID;
+    if (B == 0 || C == 0 || M == 0) return APB_OK;
+    if (!points || !idx || !vmax || !vmin || !amax || !amin || N <= 0 || K <= 0) return APB_E_INVALID;
+    if (C > 65535 || B > 65535) return APB_E_UNSUPPORTED;
+    const size_t row = (size_t)N * sizeof(float);
+    if (row > kSmemBudget) return APB_E_UNSUPPORTED;  // callers fall back to apb_group_f32 + a reduction
+    cudaStream_t st = (cudaStream_t)stream;
+    constexpr size_t kThird = 64 * 1024;
+    if (C >= 4 && 4 * row <= kThird) return launch_group_minmax<4>(points, idx, vmax, vmin, amax, amin, B, C, N, M, K, st);
+    if (C >= 2 && 2 * row <= kThird) return launch_group_minmax<2>(points, idx, vmax, vmin, amax, amin, B, C, N, M, K, st);
+    return launch_group_minmax<1>(points, idx, vmax, vmin, amax, amin, B, C, N, M, K, st);
 }
 extern "C" int apb_group_grad_f32(const float *grad_out, const int32_t *idx, float *grad_points, int B, int C,
                                   int N, int M, int K, apb_stream_t stream) {

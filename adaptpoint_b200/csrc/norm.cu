@@ -320,6 +320,45 @@ bool grid_ok(int B, int C) { return B <= 65535 && C <= 65535; }
 
 }  // namespace
 
+// vmax[r] = max_p y[r,p], arg[r] = first p attaining it.   One warp per row, 16-byte loads.
+// Used for "1x1 conv -> ReLU -> max over the points" heads (point_discriminator.py:166-191): since ReLU is monotone,
+// max(relu(y)) = relu(max(y)), so the ReLU'd activation is never materialised and the backward pass only touches the
+// arg-max columns.
+__global__ void __launch_bounds__(256) rowmax_kernel(const float *__restrict__ y, float *__restrict__ vmax,
+                                                      int32_t *__restrict__ arg, long long rows, int P) {
+    const long long r = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (r >= rows) return;
+    const int lane = threadIdx.x & 31;
+    const float *row = y + r * P;
+    float best = -INFINITY;
+    int bi = 0x7fffffff;
+    if ((P & 3) == 0 && ((reinterpret_cast<uintptr_t>(row) & 15) == 0)) {
+        for (int p = lane * 4; p < P; p += 128) {
+            const float4 v = apb_ld_nc_f4(row + p);
+            if (v.x > best) { best = v.x; bi = p; }
+            if (v.y > best) { best = v.y; bi = p + 1; }
+            if (v.z > best) { best = v.z; bi = p + 2; }
+            if (v.w > best) { best = v.w; bi = p + 3; }
+        }
+    } else {
+        for (int p = lane; p < P; p += 32) {
+            const float v = __ldg(row + p);
+            if (v > best) { best = v; bi = p; }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+    }
+    if (lane == 0) {
+        vmax[r] = best;
+        arg[r] = bi == 0x7fffffff ? 0 : bi;
+    }
+}
+
+
 extern "C" int apb_bn_stats_f32(const float *x, double *stats, int B, int C, long long P, apb_stream_t stream) {
     if (B < 0 || C < 0 || P < 0) return APB_E_INVALID;
     if (B == 0 || C == 0 || P == 0) return APB_OK;
@@ -407,6 +446,16 @@ extern "C" int apb_affine_f32(const float *x, const float *mask_relu, const floa
     if (!grid_ok(B, C)) return APB_E_UNSUPPORTED;
     dim3 grid(apb_div_up(P, CHUNK), C, B);
     affine_kernel<<<grid, NT, 0, (cudaStream_t)stream>>>(x, mask_relu, scale, shift, relu, out, C, P);
+    APB_CHECK_LAUNCH();
+    return APB_OK;
+}
+
+extern "C" int apb_rowmax_f32(const float *y, float *vmax, int32_t *arg, long long rows, int P, apb_stream_t stream) {
+    if (rows < 0 || P < 0) return APB_E_INVALID;
+    if (rows == 0) return APB_OK;
+    if (!y || !vmax || !arg || P == 0) return APB_E_INVALID;
+    if (rows > 8LL * 2147483647LL) return APB_E_UNSUPPORTED;
+    rowmax_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, (cudaStream_t)stream>>>(y, vmax, arg, rows, P);
     APB_CHECK_LAUNCH();
     return APB_OK;
 }

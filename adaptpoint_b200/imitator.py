@@ -25,7 +25,7 @@ from torch.autograd import Function
 
 from . import _cabi, ops
 from .norm import ConvBlock, TcBatchNorm1d
-from .tcconv import TcConv1d, TcConv2d
+from .tcconv import TcConv1d, TcConv2d, conv_max
 
 
 # ----------------------------------------------------------------------------------------------------------
@@ -188,11 +188,19 @@ class PointsetGrouper(nn.Module):
         new_xyz = torch.gather(xyz, 1, fps_idx.unsqueeze(-1).expand(-1, -1, 3))
         centre = torch.gather(feats, 2, fps_idx.unsqueeze(1).expand(-1, C, -1))            # (B,C,np)
         idx = ops.ball_query(self.radi, self.kneighbors, xyz, new_xyz)
-        grouped = ops.grouping_operation(feats.contiguous(), idx)                            # (B,C,np,k)
-        if self.normalize is not None:
-            mean = grouped.mean(dim=3, keepdim=True) if self.normalize == "center" else centre.unsqueeze(-1)
-            grouped = self.affine_alpha.view(1, C, 1, 1) * (grouped - mean) + self.affine_beta.view(1, C, 1, 1)
-        return new_xyz, grouped.max(dim=3)[0]
+        if self.normalize == "center":   # needs the mean over the neighbours: unfused composition
+            grouped = ops.grouping_operation(feats.contiguous(), idx)                        # (B,C,np,k)
+            grouped = self.affine_alpha.view(1, C, 1, 1) * (grouped - grouped.mean(dim=3, keepdim=True)) \
+                + self.affine_beta.view(1, C, 1, 1)
+            return new_xyz, grouped.max(dim=3)[0]
+        # alpha*(g - centre) + beta is monotone in g: its max over the neighbours is the same expression of the
+        # max (alpha >= 0) or the min (alpha < 0) of g, bit for bit, so the (B,C,np,k) tensor is never built
+        gmax, gmin = ops.group_minmax(feats.contiguous(), idx)                               # (B,C,np) each
+        if self.normalize is None:
+            return new_xyz, gmax
+        alpha, beta = self.affine_alpha.view(1, C, 1), self.affine_beta.view(1, C, 1)
+        sel = torch.where(alpha >= 0, gmax, gmin)
+        return new_xyz, alpha * (sel - centre) + beta
 
 
 class Anchor_selfattention(nn.Module):
@@ -234,7 +242,7 @@ class Producefactor(nn.Module):
         """a_points (B,A,3), sa_x (B,C,np) channel-major, sa_xyz (B,np,3) -> (B,A,9)."""
         A = a_points.shape[1]
         idx = ops.knn_query(self.keighbors, sa_xyz.contiguous(), a_points.contiguous())       # (B,A,k)
-        local = ops.grouping_operation(sa_x.contiguous(), idx).max(dim=3)[0].permute(0, 2, 1)  # (B,A,C)
+        local = ops.group_minmax(sa_x.contiguous(), idx)[0].permute(0, 2, 1)                  # (B,A,C)
         local = local + self.anchor_selfattention(x=local, xyz=a_points)
         glob = self.global_layer(a_points.permute(0, 2, 1)).permute(0, 2, 1).max(dim=1, keepdim=True)[0]
         feat = torch.cat([local, glob.repeat(1, A, 1)], dim=-1)
@@ -364,9 +372,11 @@ class PointNetSetAbstraction_SpectralNorm(nn.Module):
         """xyz (B,3,N) [, points (B,D,N)] -> (zeros (B,3,1), features (B,C,1))."""
         x = xyz if points is None else torch.cat([xyz, points], dim=1)
         x = x.unsqueeze(2)                                                    # (B,C,1,N) = permute of (B,1,N,C)
-        for conv in self.mlp_convs:
+        for conv in self.mlp_convs[:-1]:
             x = F.relu(conv(x))
-        return xyz.new_zeros(xyz.shape[0], xyz.shape[1], 1), torch.max(x, 3)[0]
+        # last layer: conv -> ReLU -> max over the points == ReLU(max over the points of the conv)
+        pooled = F.relu(conv_max(self.mlp_convs[-1], x))                          # (B,C)
+        return xyz.new_zeros(xyz.shape[0], xyz.shape[1], 1), pooled.unsqueeze(-1)
 
 
 class PointDiscriminator1(nn.Module):

@@ -123,6 +123,47 @@ class GroupingOperation(Function):
 grouping_operation = GroupingOperation.apply
 
 
+class GroupMinMax(Function):
+    @staticmethod
+    def forward(ctx, features: torch.Tensor, idx: torch.Tensor):
+        """features (B,C,N), idx (B,npoint,nsample) int32 -> (max, min) over the nsample neighbours, each (B,C,npoint):
+        grouping_operation(features, idx).max(-1)[0] / .min(-1)[0] without the (B,C,npoint,nsample) tensor
+        (apb_group_minmax_f32).  The backward pass scatters (B,C,npoint) gradients to the arg-max / arg-min points."""
+        _check(features, "features", torch.float32)
+        _check(idx, "idx", torch.int32)
+        B, M, K = idx.size()
+        _, C, N = features.size()
+        dev = features.device
+        vmax = torch.empty((B, C, M), dtype=torch.float32, device=dev)
+        vmin = torch.empty((B, C, M), dtype=torch.float32, device=dev)
+        amax = torch.empty((B, C, M), dtype=torch.int32, device=dev)
+        amin = torch.empty((B, C, M), dtype=torch.int32, device=dev)
+        _cabi.call("apb_group_minmax_f32", [features, idx, vmax, vmin, amax, amin, B, C, N, M, K], dev)
+        ctx.save_for_backward(amax, amin)
+        ctx.N = N
+        return vmax, vmin
+
+    @staticmethod
+    def backward(ctx, gmax, gmin):
+        amax, amin = ctx.saved_tensors
+        B, C, M = amax.shape
+        grad = torch.zeros((B, C, ctx.N), dtype=torch.float32, device=amax.device)
+        if gmax is not None:
+            grad.scatter_add_(2, amax.long(), gmax.detach().float().contiguous())
+        if gmin is not None:
+            grad.scatter_add_(2, amin.long(), gmin.detach().float().contiguous())
+        return grad, None
+
+
+def group_minmax(features, idx):
+    """(max, min) over the neighbours of grouping_operation(features, idx); falls back to the unfused composition of
+    our own kernels when a feature row does not fit in shared memory (N > 51200)."""
+    if features.shape[2] * 4 > 200 * 1024:
+        g = grouping_operation(features, idx)
+        return g.max(dim=3)[0], g.min(dim=3)[0]
+    return GroupMinMax.apply(features, idx)
+
+
 def torch_grouping_operation(features, idx):
     """Pure-torch grouping kept for API parity (reference group.py:120-137)."""
     all_idx = idx.reshape(idx.shape[0], -1)

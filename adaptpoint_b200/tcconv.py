@@ -128,6 +128,64 @@ class PointwiseConvFn(Function):
         return gx, gw, gb
 
 
+class PointwiseConvMaxFn(Function):
+    """pooled (B,Cout) = max over the points of (W x + b), x (B,Cin,P): the 1x1 conv runs on the tensor cores in
+    slices of <= 512 output channels, each slice is reduced by apb_rowmax_f32 and dropped, so the (B,Cout,P)
+    activation is never concatenated, ReLU'd or re-read; the backward pass touches only the arg-max columns.
+    Callers apply ReLU to the pooled result (max(relu(y)) == relu(max(y)))."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        B, cin = x.shape[0], x.shape[1]
+        P = x[0, 0].numel()
+        cout = weight.shape[0]
+        xs = x.detach().contiguous().float().view(B, cin, P)
+        w2d = weight.detach().reshape(cout, cin).float()
+        vals, args = [], []
+        for c0 in range(0, cout, _MAX_N):
+            c1 = min(cout, c0 + _MAX_N)
+            y = _gemm_rows(xs, w2d[c0:c1], None if bias is None else bias.detach()[c0:c1], B, cin, c1 - c0, P)
+            v = torch.empty((B, c1 - c0), dtype=torch.float32, device=x.device)
+            a = torch.empty((B, c1 - c0), dtype=torch.int32, device=x.device)
+            _cabi.call("apb_rowmax_f32", [y, v, a, B * (c1 - c0), P], x.device)
+            vals.append(v)
+            args.append(a)
+            del y
+        val = vals[0] if len(vals) == 1 else torch.cat(vals, 1)
+        arg = (args[0] if len(args) == 1 else torch.cat(args, 1)).long()
+        ctx.save_for_backward(xs, weight, arg)
+        ctx.has_bias = bias is not None
+        ctx.xshape = tuple(x.shape)
+        return val
+
+    @staticmethod
+    def backward(ctx, gy):
+        xs, weight, arg = ctx.saved_tensors
+        B, cin, P = xs.shape
+        cout = weight.shape[0]
+        g = gy.detach().float()
+        idx = arg.unsqueeze(1).expand(B, cin, cout)
+        gx = gw = gb = None
+        if ctx.needs_input_grad[0]:
+            w2d = weight.detach().reshape(cout, cin).float()
+            contrib = g.unsqueeze(1) * w2d.t().unsqueeze(0)                      # (B,cin,cout)
+            gx = torch.zeros_like(xs).scatter_add_(2, idx, contrib).view(ctx.xshape)
+        if ctx.needs_input_grad[1]:
+            gw = torch.einsum("bo,bio->oi", g, xs.gather(2, idx)).view(weight.shape)
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            gb = g.sum(0)
+        return gx, gw, gb
+
+
+def conv_max(mod, x):
+    """max over all positions of the 1x1 conv `mod` applied to x (B,Cin,...) -> (B,Cout); fused path on the tc
+    backend, plain torch otherwise."""
+    if _use_tc(mod, x):
+        return PointwiseConvMaxFn.apply(x, mod.weight, mod.bias)
+    y = mod(x)
+    return y.flatten(2).max(dim=2)[0]
+
+
 def _use_tc(mod, x):
     return (_BACKEND == "tc" and x.is_cuda and x.dtype == torch.float32 and mod.groups == 1
             and all(k == 1 for k in mod.kernel_size) and all(s == 1 for s in mod.stride)

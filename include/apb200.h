@@ -77,6 +77,12 @@ int apb_knn_f32(const float *new_xyz, const float *xyz, int32_t *idx, float *dis
 /* group_points_wrapper(b,c,n,npoints,nsample,points,idx,out) -- group_points.cpp:25-35 */
 int apb_group_f32(const float *points, const int32_t *idx, float *out, int B, int C, int N, int M, int K,
                   apb_stream_t stream);
+/* Grouping fused with the max and min over the K neighbours (no reference kernel; replaces
+ * grouping_operation -> normalise -> torch.max of PointsetGrouper / Producefactor, generator_component4_15.py:368-431,
+ * 560-563):  vmax/vmin (B,C,M) f32, amax/amin (B,C,M) int32 = the point index in [0,N) that attains them (first
+ * neighbour slot on ties).  APB_E_UNSUPPORTED when one feature row (4N bytes) exceeds shared memory. */
+int apb_group_minmax_f32(const float *points, const int32_t *idx, float *vmax, float *vmin, int32_t *amax,
+                         int32_t *amin, int B, int C, int N, int M, int K, apb_stream_t stream);
 /* group_points_grad_wrapper(b,c,n,npoints,nsample,grad_out,idx,grad_points) -- group_points.cpp:11-22;
  * grad_points (B,C,N) pre-zeroed. */
 int apb_group_grad_f32(const float *grad_out, const int32_t *idx, float *grad_points, int B, int C, int N,
@@ -175,6 +181,9 @@ int apb_bn_bwd_apply_f32(const float *x, const float *dy, const float *y_relu, c
                          int B, int C, long long P, apb_stream_t stream);
 int apb_kmax_stats_f32(const float *y, float *vmax, float *vmin, int32_t *arg, double *stats, int B, int C, int M,
                        int K, apb_stream_t stream);
+/* vmax[r] = max_p y[r,p], arg[r] = first p attaining it, y (rows,P) row-major.  Replaces the ReLU + torch.max over
+ * the points of the discriminator's group_all stage (point_discriminator.py:166-191): max(relu(y)) = relu(max(y)). */
+int apb_rowmax_f32(const float *y, float *vmax, int32_t *arg, long long rows, int P, apb_stream_t stream);
 int apb_bnmax_bwd_f32(const float *y, const float *gsel, const int32_t *arg, const float *a, const float *bcoef,
                       float *dy, int B, int C, int M, int K, apb_stream_t stream);
 

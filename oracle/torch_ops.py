@@ -98,6 +98,12 @@ def grouping_operation(features, idx):
 torch_grouping_operation = grouping_operation
 
 
+def group_minmax(features, idx):
+    """CPU stand-in of ops.group_minmax: the unfused composition."""
+    g = grouping_operation(features, idx)
+    return g.max(dim=3)[0], g.min(dim=3)[0]
+
+
 def gather_operation(features, idx):
     return features.gather(2, idx.long().unsqueeze(1).expand(-1, features.shape[1], -1))
 
@@ -159,6 +165,7 @@ def deform_mask(xyz, anchor, affine, proj_axis, mask=None, sigma=0.5):
 
 
 _NAMES = ["furthest_point_sample", "ball_query", "knn_query", "grouping_operation", "torch_grouping_operation",
+          "group_minmax",
           "gather_operation", "three_nn", "three_interpolate", "three_interpolation", "fps"]
 
 

@@ -1,0 +1,5 @@
+set -x
+mkdir -p gpurun_out
+timeout 300 python -m pytest tests -m gpu -x -q 2>&1 | tail -6
+timeout 300 python bench.py --steps 10 --warmup 3 > gpurun_out/bench_r01_k.json 2> gpurun_out/bench_r01_k.err; echo "bench exit $?"; cut -c1-200 gpurun_out/bench_r01_k.json; tail -3 gpurun_out/bench_r01_k.err
+timeout 200 python scripts/profile_step.py > gpurun_out/step_profile_k.txt 2>&1; head -9 gpurun_out/step_profile_k.txt

@@ -92,3 +92,46 @@ def test_model_step_tc_vs_fp32(cuda_dev):
             continue
         cos = torch.nn.functional.cosine_similarity(g.flatten(), gt.flatten(), dim=0).item()
         assert cos > 0.9, (n, cos)   # earliest layers see the compounded routing noise (0.96 measured); later ones > 0.99
+
+
+@pytest.mark.parametrize("B,cin,cout,P,bias", [(4, 128, 1024, 2048, True), (3, 64, 96, 777, False), (2, 3, 64, 100, True)])
+def test_conv_max_fused_vs_torch(cuda_dev, B, cin, cout, P, bias):
+    """tcconv.conv_max (GEMM slices -> apb_rowmax_f32, backward through the arg-max columns only) against
+    relu(conv) -> max over the points through torch autograd (point_discriminator.py:166-191)."""
+    from adaptpoint_b200 import tcconv
+    gen = torch.Generator().manual_seed(P)
+    conv = tcconv.TcConv2d(cin, cout, 1, bias=bias).to(cuda_dev)
+    x = torch.randn(B, cin, 1, P, generator=gen).to(cuda_dev).requires_grad_(True)
+    gy = torch.randn(B, cout, generator=gen).to(cuda_dev)
+    with tcconv.conv_backend("torch"):
+        want = torch.relu(conv(x)).flatten(2).max(dim=2)[0]
+        want.backward(gy)
+    ref = [x.grad.clone(), conv.weight.grad.clone(), None if not bias else conv.bias.grad.clone()]
+    x.grad = None
+    conv.zero_grad()
+    with tcconv.conv_backend("tc"):
+        got = torch.relu(tcconv.conv_max(conv, x))
+        got.backward(gy)
+    assert got.shape == want.shape
+    assert _rel(got, want) < 3e-3
+    # tf32 rounding can move an arg-max between near-tied columns: compare gradients in aggregate
+    cos = torch.nn.functional.cosine_similarity
+    assert cos(x.grad.flatten(), ref[0].flatten(), dim=0) > 0.98
+    assert cos(conv.weight.grad.flatten(), ref[1].flatten(), dim=0) > 0.98
+    if bias:
+        assert _rel(conv.bias.grad, ref[2]) < 1e-4
+
+
+def test_rowmax_exact(cuda_dev):
+    """apb_rowmax_f32: bit-exact max and FIRST arg-max per row, incl. ties, odd P and unaligned rows."""
+    from adaptpoint_b200 import _cabi
+    gen = torch.Generator().manual_seed(3)
+    for rows, P in ((64, 2048), (37, 777), (5, 3), (1, 1)):
+        y = torch.randint(-8, 8, (rows, P), generator=gen).float().to(cuda_dev)     # many exact ties
+        v = torch.empty(rows, device=cuda_dev)
+        a = torch.empty(rows, dtype=torch.int32, device=cuda_dev)
+        _cabi.call("apb_rowmax_f32", [y, v, a, rows, P], cuda_dev)
+        want_v = y.max(dim=1)[0]
+        first = (y == want_v[:, None]).float().argmax(dim=1)
+        assert torch.equal(v, want_v)
+        assert torch.equal(a.long(), first)
