@@ -41,6 +41,8 @@ _SIGNATURES = {
     "apb_bn_bwd_reduce_f32": [_p, _p, _p, _p, _p, _p, _i, _i, _ll, _p],
     "apb_bn_bwd_apply_f32": [_p, _p, _p, _p, _p, _p, _p, _d, _p, _i, _i, _ll, _p],
     "apb_kmax_stats_f32": [_p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
+    "apb_attn_fwd_f32": [_p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
+    "apb_attn_bwd_f32": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
     "apb_rowmax_f32": [_p, _p, _p, _ll, _i, _p],
     "apb_bnmax_bwd_f32": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
     "apb_sa_fused_fwd_bf16": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _i, _p, _p,

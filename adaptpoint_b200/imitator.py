@@ -222,9 +222,12 @@ class Anchor_selfattention(nn.Module):
         rel = xyz - xyz.mean(dim=1, keepdim=True)
         emb = self.pos_embedding(rel.permute(0, 2, 1)).permute(0, 2, 1)
         q, k, v = self.to_qkv(x).chunk(3, dim=-1)
-        split = lambda t: (t + emb).reshape(B, M, self.head_num, self.head_dim).permute(0, 2, 1, 3)
-        o = F.scaled_dot_product_attention(split(q), split(k), split(v))
-        o = o.permute(0, 2, 1, 3).reshape(B, M, -1)
+        if x.is_cuda and self.head_dim == 16:      # our flash-style fp32 kernel, token-major in and out
+            o = ops.self_attention(q + emb, k + emb, v + emb, self.head_num)
+        else:
+            split = lambda t: (t + emb).reshape(B, M, self.head_num, self.head_dim).permute(0, 2, 1, 3)
+            o = F.scaled_dot_product_attention(split(q), split(k), split(v))
+            o = o.permute(0, 2, 1, 3).reshape(B, M, -1)
         return self.res(o.permute(0, 2, 1)).permute(0, 2, 1)
 
 

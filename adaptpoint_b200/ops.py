@@ -164,6 +164,37 @@ def group_minmax(features, idx):
     return GroupMinMax.apply(features, idx)
 
 
+class SelfAttention16(Function):
+    @staticmethod
+    def forward(ctx, q, k, v, heads: int):
+        """q,k,v (B,M,heads*16) f32 token-major -> softmax(q k^T / 4) v, (B,M,heads*16); scores stay in registers
+        (apb_attn_fwd_f32; reference generator_component4_15.py:434-480)."""
+        q, k, v = (t.detach().contiguous().float() for t in (q, k, v))
+        B, M, C = q.shape
+        o = torch.empty_like(q)
+        lse = torch.empty((B, heads, M), dtype=torch.float32, device=q.device)
+        _cabi.call("apb_attn_fwd_f32", [q, k, v, o, lse, B, M, heads, C // heads], q.device)
+        ctx.save_for_backward(q, k, v, o, lse)
+        ctx.heads = heads
+        return o
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        q, k, v, o, lse = ctx.saved_tensors
+        B, M, C = q.shape
+        go = grad_out.detach().contiguous().float()
+        dq, dk, dv = torch.empty_like(q), torch.empty_like(q), torch.empty_like(q)
+        delta = torch.empty_like(lse)
+        _cabi.call("apb_attn_bwd_f32", [q, k, v, o, go, lse, dq, dk, dv, delta, B, M, ctx.heads, C // ctx.heads],
+                   q.device)
+        return dq, dk, dv, None
+
+
+def self_attention(q, k, v, heads):
+    """Multi-head self-attention over (B,M,C) token-major tensors, head_dim = C/heads = 16."""
+    return SelfAttention16.apply(q, k, v, heads)
+
+
 def torch_grouping_operation(features, idx):
     """Pure-torch grouping kept for API parity (reference group.py:120-137)."""
     all_idx = idx.reshape(idx.shape[0], -1)

@@ -187,6 +187,16 @@ int apb_rowmax_f32(const float *y, float *vmax, int32_t *arg, long long rows, in
 int apb_bnmax_bwd_f32(const float *y, const float *gsel, const int32_t *arg, const float *a, const float *bcoef,
                       float *dy, int B, int C, int M, int K, apb_stream_t stream);
 
+/* Multi-head self-attention of the imitator (generator_component4_15.py:434-480, Anchor_selfattention.forward:
+ * attn = softmax(q k^T / sqrt(d)); out = attn v), head_dim = 16 only (APB_E_UNSUPPORTED otherwise), fp32, scores never
+ * materialised.  q,k,v,o,dout,dq,dk,dv: (B, M, H*16) token-major, 16-byte aligned; lse, delta: (B,H,M) f32 (lse =
+ * log2-domain log-sum-exp written by the forward pass; delta = caller-allocated workspace of the backward pass). */
+int apb_attn_fwd_f32(const float *q, const float *k, const float *v, float *o, float *lse, int B, int M, int H,
+                     int head_dim, apb_stream_t stream);
+int apb_attn_bwd_f32(const float *q, const float *k, const float *v, const float *o, const float *dout,
+                     const float *lse, float *dq, float *dk, float *dv, float *delta, int B, int M, int H,
+                     int head_dim, apb_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
