@@ -66,7 +66,11 @@ def feedback_loss(classifier, criterion, data_real, data_fake, rho):
     (ganloss_cls.py:31-65)."""
     classifier.eval()
     pred_fake = classifier(data_fake)
-    pred_real = classifier(data_real)
+    if data_real["pos"].requires_grad or data_real["x"].requires_grad or any(p.requires_grad for p in classifier.parameters()):
+        pred_real = classifier(data_real)
+    else:   # nothing upstream of the real batch takes a gradient: plain inference (the fused bf16 SA kernels when
+        with torch.no_grad():   # the classifier was built with fused=True)
+            pred_real = classifier(data_real)
     label = data_real["y"].long()
     loss_fake, loss_real = criterion(pred_fake, label), criterion(pred_real, label)
     return torch.abs(1 - torch.exp(loss_fake - rho * loss_real)).mean()
@@ -100,12 +104,13 @@ class AdaptPointTrainer:
                     dist.broadcast(t.data, 0)
         ap = self.cfg["adaptpoint_params"]
         cap = self.device.type == "cuda"      # device-side step counters: required inside a CUDA graph
+        kw = {"capturable": True, "fused": True} if cap else {}   # one multi-tensor kernel per optimizer step
         self.opt_c = torch.optim.AdamW(self.classifier.parameters(), lr=self.cfg["lr"],
-                                       weight_decay=self.cfg["weight_decay"], capturable=cap)
+                                       weight_decay=self.cfg["weight_decay"], **kw)
         self.opt_g = torch.optim.Adam(self.generator.parameters(), lr=ap["lr_generator"], betas=(ap["b1"], ap["b2"]),
-                                      capturable=cap)
+                                      **kw)
         self.opt_d = torch.optim.Adam(self.discriminator.parameters(), lr=ap["lr_discriminator"],
-                                      betas=(ap["b1"], ap["b2"]), capturable=cap)
+                                      betas=(ap["b1"], ap["b2"]), **kw)
         self.criterion_gan = nn.BCELoss()
         self.criterion = SmoothCrossEntropy(label_smoothing=self.cfg["label_smoothing"])
         self.pointwolf = PointWOLF_classversion(**self.cfg["pointwolf"])

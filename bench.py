@@ -95,8 +95,36 @@ def alg_bytes(name, a):
     if name == "apb_pwconv_wgrad_tf32":
         B, Cin, Cout, P = a
         return 4.0 * B * P * (Cin + Cout)
-    if name.startswith("apb_sa_fused"):
-        return None
+    # streaming normalisation / pooling kernels (csrc/norm.cu): one pass over the (B,C,P) activation per operand
+    if name == "apb_bn_stats_f32":
+        B, C, P = a
+        return 4.0 * B * C * P
+    if name == "apb_bn_apply_f32":
+        _relu, B, C, P = a
+        return 8.0 * B * C * P
+    if name == "apb_bn_bwd_reduce_f32":
+        B, C, P = a
+        return 8.0 * B * C * P
+    if name == "apb_bn_bwd_apply_f32":
+        B, C, P = a
+        return 12.0 * B * C * P
+    if name == "apb_affine_f32":
+        _relu, B, C, P = a
+        return 8.0 * B * C * P
+    if name == "apb_kmax_stats_f32":
+        B, C, M, K = a
+        return 4.0 * B * C * M * (K + 3)
+    if name == "apb_bnmax_bwd_f32":
+        B, C, M, K = a
+        return 4.0 * B * C * M * (K + 2)
+    if name == "apb_rowmax_f32":
+        rows, P = a
+        return 4.0 * rows * (P + 2)
+    if name == "apb_group_minmax_f32":
+        B, C, N, M, K = a
+        return 4.0 * B * (C * N + M * K + 4 * C * M)
+    # apb_attn_*: fp32-issue / MUFU bound (32 FMA + 1 exp2 per score), no HBM or tensor roofline; apb_sa_fused_*:
+    # reported by benchmarks/bench_sa.py against the tensor pipe
     return None
 
 
@@ -206,7 +234,7 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
     _cabi.load()
 
-    tr = AdaptPointTrainer(device=dev, seed=0, conv_backend=args.conv)
+    tr = AdaptPointTrainer(device=dev, seed=0, conv_backend=args.conv, fused_eval=args.fused_eval)
     pts_h, y_h = loader_batch(B_PER_GPU, N_POINTS, 100 + rank)
     pts_pin, y_pin = pts_h.pin_memory(), y_h.pin_memory()
     loss_pin = torch.empty(3, dtype=torch.float32).pin_memory()
@@ -287,12 +315,37 @@ def run_ours(args):
             v[0] = v[0] * args.steps // trace_steps
             v[1] = v[1] * args.steps / trace_steps
         table = sorted(((k, v) for k, v in agg.items()), key=lambda kv: -kv[1][1])
-        (dname, dargs), (dcount, dms) = table[0]
-        ab = alg_bytes(dname, dargs)
+        # kernel families (one C-ABI entry point = one kernel family); the roofline object describes the family that
+        # takes the most time among those with an HBM roofline model (algorithmic bytes per launch, alg_bytes())
+        fam = {}
+        for (name, a), (cnt, ms) in agg.items():
+            f = fam.setdefault(name, {"launches": 0, "ms": 0.0, "bytes": 0.0, "modelled": True, "top": None})
+            f["launches"] += cnt
+            f["ms"] += ms
+            ab1 = alg_bytes(name, a)
+            if ab1 is None:
+                f["modelled"] = False
+            else:
+                f["bytes"] += ab1 * cnt
+            if f["top"] is None or ms > f["top"][1]:
+                f["top"] = (a, ms, cnt)
+        fams = sorted(fam.items(), key=lambda kv: -kv[1]["ms"])
+        dname, dfam = next(((n, f) for n, f in fams if f["modelled"]), fams[0])
+        dcount, dms = dfam["launches"], dfam["ms"]
+        dargs = dfam["top"][0]
+        ab = dfam["bytes"] / dcount if dfam["modelled"] else None
         avg_s = dms / dcount / 1e3
         achieved = ab / 1e9 / avg_s if ab else None
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+        if os.path.exists(tpath):
+            traffic = json.load(open(tpath)).get(dname + "|" + ",".join(str(x) for x in dargs))
         kern = [{"call": k[0], "dims": list(k[1]), "launches": v[0], "ms_total": round(v[1], 3),
                  "share_of_step": round(v[1] / ms_total, 4)} for k, v in table[:8]]
+        famlist = [{"call": n, "launches": f["launches"], "ms_total": round(f["ms"], 3),
+                    "share_of_step": round(f["ms"] / ms_total, 4),
+                    "hbm_frac": round(f["bytes"] / 1e9 / (f["ms"] / 1e3) / hbm, 4) if f["modelled"] and f["ms"] > 0 else None}
+                   for n, f in fams[:10]]
         samples = world * B_PER_GPU * args.steps
         out = {
             "metric": METRIC, "value": round(samples / (ms_total / 1e3), 2), "unit": UNIT, "n_gpus": world,
@@ -302,7 +355,9 @@ def run_ours(args):
             "config": {"workload": WORKLOAD, "global_batch": world * B_PER_GPU, "parallelism": f"dp{world}",
                        "precision": ("1x1 convs: tf32 operands (fwd, dgrad, wgrad), fp32 accumulate, tcgen05 (= the reference's "
                                      "default cuDNN allow_tf32); "
-                                     "everything else fp32" if args.conv == "tc" else "strict fp32 (cuDNN, TF32 off)"),
+                                     "everything else fp32" if args.conv == "tc" else "strict fp32 (cuDNN, TF32 off)")
+                                    + ("; no-grad classifier pass of the feedback loss: fused bf16 SA kernels (2e-2)"
+                                       if args.fused_eval else ""),
                        "cuda_graph": bool(args.graph),
                        "kernel_trace": f"C-ABI launches timed with CUDA events over {trace_steps} eager steps before "
                                        "the timed region (same kernels the graph replays), scaled to K steps",
@@ -312,14 +367,18 @@ def run_ours(args):
                     "h2d_bytes_per_step": pts_pin.numel() * 4 + y_pin.numel() * 8, "d2h_bytes_per_step": 12},
             "gpu_launches": launches,
             "clocks": clocks,
-            "roofline": {"bound": "hbm", "kernel": dname, "dims": list(dargs), "achieved": None if achieved is None
+            "roofline": {"bound": "hbm", "kernel": dname, "dims": list(dargs),
+                         "dims_note": "family aggregate over all its launches in the step (achieved = sum of algorithmic "
+                                      "bytes / sum of durations); dims = the member with the most time; traffic = ncu "
+                                      "dram bytes of that member (profiles/ncu_traffic.json)",
+                         "achieved": None if achieved is None
                          else round(achieved, 1), "peak": hbm, "unit": "GB/s", "frac": None if achieved is None
-                         else round(achieved / hbm, 4), "traffic": None, "peak_source": peak_src,
+                         else round(achieved / hbm, 4), "traffic": traffic, "peak_source": peak_src,
                          "avg_launch_us": round(avg_s * 1e6, 2), "launches": dcount,
                          "share_of_step": round(dms / ms_total, 4),
                          "algorithmic_bytes_per_launch": ab},
             "our_kernels": {"ms_total": round(ours_ms, 3), "share_of_step": round(ours_ms / ms_total, 4),
-                            "top": kern},
+                            "top": kern, "families": famlist},
         }
         if world == 1 and not args.no_cpu:
             sample_B = 4
@@ -341,6 +400,9 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--conv", default="tc", choices=["tc", "torch"], help="1x1-conv backend (tcgen05 kernels / cuDNN fp32)")
     ap.add_argument("--no-graph", dest="graph", action="store_false", help="eager launches instead of one CUDA graph")
+    ap.add_argument("--no-fused-eval", dest="fused_eval", action="store_false",
+                    help="classifier inference on the real batch (feedback loss) through the unfused fp32 modules "
+                         "instead of the fused bf16 set-abstraction kernels")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
