@@ -48,7 +48,9 @@ enum Epilogue { EPI_STORE_CM = 0, EPI_STORE_PM = 1, EPI_KMAX = 2 };
 struct TcParams {
     long long rows;   // valid rows: B*P (channel-major loader) or B*M*K (gather loader)
     int kchunks;      // padded reduction length / 64
-    int Cout;         // valid output channels
+    int Cout;         // valid output channels (all slices together)
+    int nslice;       // output channels per CTA column (blockIdx.y); == NCP.  One slice unless the row tiles alone
+                      // cannot fill the SMs (launch_tc), then Cout is cut into slices of <= 256 channels
     int NCP;          // Cout rounded up to 16 (UMMA N granularity), <= 512
     int wrows;        // weight rows resident per stage: NCP if <= 256 else 512
     int stages;       // smem ring depth
@@ -100,6 +102,8 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
     const int acc_stages = p.NCP <= 256 ? 2 : 1;
     const uint32_t spg = p.stages / NGROUPS;  // smem stages per producer group
     const long long ntiles = (p.rows + BM - 1) / BM;
+    const int n0 = blockIdx.y * p.nslice;            // first output channel of this CTA's slice
+    const int Cout = min(p.nslice, p.Cout - n0);     // valid channels of the slice
 
     if (warp == 0 && lane == 0) {
         tc::tma_prefetch_desc(&wmap);
@@ -126,9 +130,9 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
     }
     if (tid >= EPI0) {
         for (int c = tid - EPI0; c < 512; c += 128) {
-            const bool ok = p.scale != nullptr && c < p.Cout;
-            ep_ss[c] = ok ? p.scale[c] : 1.f;
-            ep_ss[512 + c] = ok ? p.shift[c] : 0.f;
+            const bool ok = p.scale != nullptr && c < Cout;
+            ep_ss[c] = ok ? p.scale[n0 + c] : 1.f;
+            ep_ss[512 + c] = ok ? p.shift[n0 + c] : 0.f;
         }
     }
     tc::tc_fence_before();
@@ -149,8 +153,8 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
                     tc::mbar_wait(&empty_bar[s], ph ^ 1);
                     uint8_t *wdst = smem + (size_t)s * stage_bytes + A_BYTES;
                     tc::mbar_arrive_expect_tx(&full_bar[s], (uint32_t)p.wrows * 128);
-                    tc::tma_load_2d(wdst, &wmap, kc * BKE, 0, &full_bar[s]);
-                    if (p.wrows > 256) tc::tma_load_2d(wdst + 256 * 128, &wmap, kc * BKE, 256, &full_bar[s]);
+                    tc::tma_load_2d(wdst, &wmap, kc * BKE, n0, &full_bar[s]);
+                    if (p.wrows > 256) tc::tma_load_2d(wdst + 256 * 128, &wmap, kc * BKE, n0 + 256, &full_bar[s]);
                 }
             }
         }
@@ -354,7 +358,7 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
                 const long long q = (tile * BM + q4 * 32) / p.K;  // b*M + m
                 const bool qvalid = (tile * BM + q4 * 32) < p.rows;
                 const long long b = q / p.M, m = q - b * p.M;
-                float *out = p.Y + (b * p.Cout) * p.M + m;
+                float *out = p.Y + (b * p.Cout + n0) * p.M + m;
                 for (int cb = 0; cb < p.NCP; cb += 32) {
                     uint32_t v[32];
                     tc::tmem_ld_32x32(tacc + cb, v);
@@ -367,7 +371,7 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
                         if (lane == j) mine = r;
                     }
                     const int c = cb + lane;
-                    if (qvalid && c < p.Cout) {
+                    if (qvalid && c < Cout) {
                         float x = tc::ordered_to_float(mine);
                         if (p.relu) x = fmaxf(x, 0.f);
                         out[(size_t)c * p.M] = x;
@@ -376,7 +380,7 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
             } else {
                 const long long b = valid ? grow / p.P : 0;
                 const long long pp = valid ? grow - b * p.P : 0;
-                float *ycm = p.Y + (b * p.Cout) * p.P + pp;  // EPI_STORE_CM: lanes = consecutive points (coalesced)
+                float *ycm = p.Y + (b * p.Cout + n0) * p.P + pp;  // EPI_STORE_CM: lanes = consecutive points (coalesced)
                 for (int cb = 0; cb < p.NCP; cb += 32) {
                     uint32_t v[32];
                     tc::tmem_ld_32x32(tacc + cb, v);
@@ -389,7 +393,7 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
                     }
                     if (EPI == EPI_STORE_CM) {
                         if (valid) {
-                            if (cb + 32 <= p.Cout) {
+                            if (cb + 32 <= Cout) {
 #pragma unroll
                                 for (int j = 0; j < 32; ++j) {
                                     *ycm = x[j];
@@ -398,21 +402,21 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
                             } else {
 #pragma unroll
                                 for (int j = 0; j < 32; ++j) {
-                                    if (cb + j < p.Cout) *ycm = x[j];
+                                    if (cb + j < Cout) *ycm = x[j];
                                     ycm += p.P;
                                 }
                             }
                         }
                     } else if (valid) {
-                        float *y = p.Y + grow * p.Cout + cb;       // one 128-byte line per thread
-                        if (cb + 32 <= p.Cout && (p.Cout & 3) == 0) {
+                        float *y = p.Y + grow * p.Cout + n0 + cb;  // one 128-byte line per thread
+                        if (cb + 32 <= Cout && (p.Cout & 3) == 0) {
 #pragma unroll
                             for (int j = 0; j < 32; j += 4)
                                 *reinterpret_cast<float4 *>(y + j) = make_float4(x[j], x[j + 1], x[j + 2], x[j + 3]);
                         } else {
 #pragma unroll
                             for (int j = 0; j < 32; ++j)
-                                if (cb + j < p.Cout) y[j] = x[j];
+                                if (cb + j < Cout) y[j] = x[j];
                         }
                     }
                 }
@@ -531,6 +535,20 @@ int launch_tc(TcParams p, const void *Wb, int Kp, cudaStream_t st) {
     if ((reinterpret_cast<uintptr_t>(Wb) & 15) != 0) return APB_E_INVALID;
     p.kchunks = Kp / BKE;
     p.NCP = (p.Cout + 15) / 16 * 16;
+    // Few row tiles (deep stages: B*P <= a few thousand rows) leave most SMs idle and make one CTA stream the whole
+    // weight matrix: cut Cout into slices of >= 64 channels until the grid covers the SMs.
+    const long long ntiles = (p.rows + BM - 1) / BM;
+    int nsplit = 1;
+    if (ntiles * 2 <= APB_NUM_SMS && p.Cout >= 128) {
+        nsplit = (int)(APB_NUM_SMS / ntiles);
+        if (nsplit > p.Cout / 64) nsplit = p.Cout / 64;
+        if (nsplit < 1) nsplit = 1;
+    }
+    if (nsplit > 1) {
+        p.NCP = ((p.Cout + nsplit - 1) / nsplit + 15) / 16 * 16;
+        nsplit = (p.Cout + p.NCP - 1) / p.NCP;
+    }
+    p.nslice = p.NCP;
     p.wrows = p.NCP <= 256 ? p.NCP : 512;
     const int stage_bytes = A_BYTES + p.wrows * 128;
     const size_t extra = 1024 /*align slack*/ + 256 /*barriers*/ +
@@ -546,8 +564,7 @@ int launch_tc(TcParams p, const void *Wb, int Kp, cudaStream_t st) {
     if (rc != APB_OK) return rc;
     auto kern = tc_rows_gemm_kernel<LOADER, EPI, TF32>;
     APB_CUDA(cudaFuncSetAttribute((const void *)kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const long long ntiles = (p.rows + BM - 1) / BM;
-    const int grid = (int)(ntiles < APB_NUM_SMS ? ntiles : APB_NUM_SMS);
+    const dim3 grid((unsigned)(ntiles < APB_NUM_SMS ? ntiles : APB_NUM_SMS), (unsigned)nsplit);
     kern<<<grid, NTHREADS, smem, st>>>(map, p);
     APB_CHECK_LAUNCH();
     return APB_OK;
