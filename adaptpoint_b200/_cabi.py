@@ -20,6 +20,8 @@ _d, _ll = ctypes.c_double, ctypes.c_longlong
 _SIGNATURES = {
     "apb_fps_f32": [_p, _p, _p, _i, _i, _i, _p],
     "apb_tune_group": [_i, _i],
+    "apb_tune_group_grad": [_i],
+    "apb_tune_group_seg": [_i],
     "apb_gather_f32": [_p, _p, _p, _i, _i, _i, _i, _p],
     "apb_gather_grad_f32": [_p, _p, _p, _i, _i, _i, _i, _p],
     "apb_ball_query_f32": [_p, _p, _p, _i, _i, _i, _f, _i, _p],
@@ -92,6 +94,20 @@ def tune_group(channels_per_cta=0, threads=0):
     status = load().apb_tune_group(int(channels_per_cta), int(threads))
     if status != 0:
         raise ApbError(f"apb_tune_group({channels_per_cta}, {threads}) rejected")
+
+
+def tune_group_grad(mode=0):
+    """Benchmarks only: grouping / three_interpolate backward path (0 automatic, 1 L2 reductions, 2 shared rows)."""
+    status = load().apb_tune_group_grad(int(mode))
+    if status != 0:
+        raise ApbError(f"apb_tune_group_grad({mode}) rejected")
+
+
+def tune_group_seg(kb=0):
+    """Benchmarks only: slice size (KB) of the sliced grouping kernels (rows longer than shared memory)."""
+    status = load().apb_tune_group_seg(int(kb))
+    if status != 0:
+        raise ApbError(f"apb_tune_group_seg({kb}) rejected")
 
 
 def fps_block_size(n):

@@ -119,7 +119,14 @@ def main():
                 rms = None
                 if ref_ok:
                     rms, _ = timeit(lambda: refcuda.group(feat, nbr), max(2, args.iters // 2), warm=1)
-                emit(f"group_C{C}", ms, mn, 4.0 * B * (C * N + M * K + C * M * K), rms)
+                extra = None
+                if N * 4 > 200 * 1024:             # cluster (DSMEM) kernel vs the direct L2 gather it replaces
+                    from adaptpoint_b200 import _cabi
+                    _cabi.tune_group(-1, 0)
+                    ms_d, _ = timeit(lambda: ops.grouping_operation(feat, nbr), max(2, args.iters // 2), flush=flush)
+                    _cabi.tune_group(0, 0)
+                    extra = {"ms_direct_l2_gather": round(ms_d, 4)}
+                emit(f"group_C{C}", ms, mn, 4.0 * B * (C * N + M * K + C * M * K), rms, extra)
             if "group_grad" in want:
                 go = torch.randn(B, C, M, K, device=dev)
                 gp = torch.zeros(B, C, N, device=dev)
@@ -132,7 +139,11 @@ def main():
                 rms = None
                 if ref_ok:
                     rms, _ = timeit(lambda: refcuda.group_grad(go, nbr, N), max(2, args.iters // 2), warm=1)
-                emit(f"group_grad_C{C}", ms, mn, 4.0 * B * (C * M * K + M * K + C * N), rms)
+                _cabi.tune_group_grad(1)           # the reference's scheme in our code: scattered L2 reductions
+                ms1, _ = timeit(bwd, max(2, args.iters // 2), flush=flush)
+                _cabi.tune_group_grad(0)
+                emit(f"group_grad_C{C}", ms, mn, 4.0 * B * (C * M * K + M * K + C * N), rms,
+                     {"ms_l2_reductions": round(ms1, 4)})
                 del go, gp
             if "gather" in want and C in (3, 128):
                 ms, mn = timeit(lambda: ops.gather_operation(feat, idx), args.iters, flush=flush)

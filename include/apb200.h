@@ -51,8 +51,15 @@ int apb_fps_block_size(int n);
 int apb_fps_f32(const float *xyz, float *temp, int32_t *idx, int B, int N, int m, apb_stream_t stream);
 
 /* Benchmarks only: override the forward grouping/gather work split (channels staged per CTA in
- * {0,1,2,4}, threads per CTA in {0,256,512,1024}; 0 = automatic).  No reference counterpart. */
+ * {0,1,2,4}, threads per CTA in {0,256,512,1024}; 0 = automatic; channels -1 = rows longer than shared
+ * memory use the direct L2 gather instead of the cluster kernel).  No reference counterpart. */
 int apb_tune_group(int channels_per_cta, int threads);
+/* Benchmarks only: backward path of grouping / three_interpolate: 0 = automatic, 1 = scattered L2
+ * reductions (the reference's scheme), 2 = accumulator rows in shared memory.  No reference counterpart. */
+int apb_tune_group_grad(int mode);
+/* Benchmarks only: slice size in KB (16..200, 0 = automatic) of the sliced grouping kernels used when a row is
+ * longer than one SM's shared memory.  No reference counterpart. */
+int apb_tune_group_seg(int kb);
 
 /* gather_points_wrapper(b,c,n,npoints,points,idx,out)      -- sampling.cpp:11-22 */
 int apb_gather_f32(const float *points, const int32_t *idx, float *out, int B, int C, int N, int m,

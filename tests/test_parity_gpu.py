@@ -113,7 +113,9 @@ def test_ball_query_full_size_vs_reference(cuda_dev, B, N, M, radius, K):
 
 
 GROUP_CASES = [(2, 35, 1024, 512, 32), (2, 3, 2048, 1024, 24), (1, 67, 512, 256, 32), (2, 5, 100, 33, 7),
-               (1, 259, 128, 64, 32), (1, 2, 60000, 100, 8), (2, 1, 17, 5, 3), (1, 6, 999, 250, 20)]
+               (1, 259, 128, 64, 32), (1, 2, 60000, 100, 8), (2, 1, 17, 5, 3), (1, 6, 999, 250, 20),
+               # rows longer than one SM's shared memory: sliced kernels with 2 / 3 / 5 slices (aligned and unaligned)
+               (2, 3, 100000, 25000, 32), (1, 3, 120001, 40000, 7), (1, 2, 250000, 32768, 16), (1, 2, 60000, 20000, 8)]
 
 
 @pytest.mark.parametrize("B,C,N,M,K", GROUP_CASES)
@@ -133,6 +135,43 @@ def test_group_fwd_bwd(cuda_dev, B, C, N, M, K):
     if refcuda.available():
         assert torch.equal(got.detach(), refcuda.group(fd.detach(), idd))
         _assert_close_rel(refcuda.group_grad(_dev(go, cuda_dev), idd, N).cpu().numpy(), want_g)
+
+
+@pytest.mark.parametrize("mode", [1, 2])
+@pytest.mark.parametrize("B,C,N,M,K", [(2, 35, 1024, 512, 32), (2, 5, 101, 33, 7), (1, 3, 16384, 4096, 32), (1, 9, 30000, 700, 16),
+                                       (1, 2, 70001, 30000, 6)])
+def test_group_grad_both_paths_accumulate(cuda_dev, B, C, N, M, K, mode):
+    """Both backward schemes (scattered L2 reductions = the reference's, group_points_gpu.cu:14-31; accumulator rows in
+    shared memory) ADD into the caller's buffer, as the reference's atomicAdd does; tolerance 1e-5 relative."""
+    from adaptpoint_b200 import _cabi
+    g = torch.Generator().manual_seed(N + mode)
+    idx = torch.randint(0, N, (B, M, K), generator=g, dtype=torch.int32)
+    idx[:, :, K // 2:] = idx[:, :, :1]          # ball-query style padding: heavy duplicates inside a row
+    go = torch.randn(B, C, M, K, generator=g)
+    base = torch.randn(B, C, N, generator=g)
+    want = base.numpy() + orc.group_grad(go.numpy(), idx.numpy(), N)
+    acc = _dev(base, cuda_dev).clone()
+    _cabi.tune_group_grad(mode)
+    try:
+        _cabi.call("apb_group_grad_f32", [_dev(go, cuda_dev), _dev(idx, cuda_dev), acc, B, C, N, M, K], acc.device)
+    finally:
+        _cabi.tune_group_grad(0)
+    _assert_close_rel(acc.cpu().numpy(), want)
+
+
+def test_group_grad_full_size_conserves_mass(cuda_dev):
+    """cfg3 size (B=32, N=16384, M=4096, K=32, C=32): per (cloud, channel) the scattered gradient sums to the sum of
+    grad_out (size-independent property; the oracle would take minutes here)."""
+    B, C, N, M, K = 32, 32, 16384, 4096, 32
+    g = torch.Generator(device=cuda_dev).manual_seed(3)
+    idx = torch.randint(0, N, (B, M, K), generator=g, dtype=torch.int32, device=cuda_dev)
+    go = torch.rand(B, C, M, K, generator=g, device=cuda_dev)
+    feat = torch.zeros(B, C, N, device=cuda_dev, requires_grad=True)
+    ops.grouping_operation(feat, idx).backward(go)
+    got, want = feat.grad.double().sum(-1), go.double().sum((-1, -2))
+    assert torch.allclose(got, want, rtol=1e-5)
+    hist = torch.zeros(B, N, device=cuda_dev).scatter_add_(1, idx.view(B, -1).long(), go[:, 0].reshape(B, -1))
+    assert torch.allclose(feat.grad[:, 0], hist, rtol=1e-5, atol=1e-5)
 
 
 @pytest.mark.parametrize("B,C,N,m", [(2, 128, 2048, 512), (2, 3, 10000, 4096), (1, 7, 33, 33), (2, 64, 1024, 1)])
