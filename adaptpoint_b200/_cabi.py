@@ -47,10 +47,15 @@ _SIGNATURES = {
     "apb_attn_bwd_f32": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
     "apb_rowmax_f32": [_p, _p, _p, _ll, _i, _p],
     "apb_bnmax_bwd_f32": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
+    "apb_peer_ws_create": [_p, _p],
+    "apb_peer_ws_open": [_p, _p],
+    "apb_peer_ws_close": [_p, _i],
+    "apb_peer_allreduce": [_p, _i, _i, _p, _i, _i, _p],
     "apb_sa_fused_fwd_bf16": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _i, _p, _p,
                               _i, _i, _i, _i, _i, _i, _i, _i, _i, _p],
 }
-EXPORTED_SYMBOLS = sorted(list(_SIGNATURES) + ["apb_version", "apb_error_string", "apb_fps_block_size"])
+EXPORTED_SYMBOLS = sorted(list(_SIGNATURES) + ["apb_version", "apb_error_string", "apb_fps_block_size",
+                                                  "apb_peer_ws_bytes", "apb_peer_max_elems"])
 
 
 class ApbError(RuntimeError):
@@ -81,6 +86,9 @@ def load():
     lib.apb_error_string.argtypes = [_i]
     lib.apb_fps_block_size.restype = _i
     lib.apb_fps_block_size.argtypes = [_i]
+    for name in ("apb_peer_ws_bytes", "apb_peer_max_elems"):
+        getattr(lib, name).restype = _i
+        getattr(lib, name).argtypes = []
     _lib = lib
     return lib
 

@@ -20,6 +20,7 @@ import torch.nn.functional as F
 from torch.autograd import Function
 
 from . import _cabi
+from . import peer
 from . import tcconv
 
 
@@ -33,7 +34,11 @@ def _dims(x):
 
 def _allreduce(t, group):
     if group is not None and dist.is_initialized() and dist.get_world_size(group) > 1:
-        dist.all_reduce(t, group=group)
+        ctx = peer.get(group)
+        if ctx is not None and ctx.supports(t):
+            ctx.allreduce_(t)            # one single-CTA kernel over NVLink peer memory (csrc/peer.cu)
+        else:
+            dist.all_reduce(t, group=group)
         return dist.get_world_size(group)
     return 1
 

@@ -21,7 +21,7 @@ import torch
 import torch.distributed as dist
 import torch.nn as nn
 
-from . import norm, ops, tcconv
+from . import norm, ops, peer, tcconv
 from .imitator import AdaptPoint_Augmentor, PointDiscriminator1, PointWOLF_classversion
 from .models import SmoothCrossEntropy, build_model
 
@@ -49,10 +49,13 @@ def allreduce_grads(params, bucket=None):
     if not grads:
         return
     flat = torch._utils._flatten_dense_tensors(grads)
-    dist.all_reduce(flat, op=dist.ReduceOp.SUM)
-    flat.div_(world)
-    for g, s in zip(grads, torch._utils._unflatten_dense_tensors(flat, grads)):
-        g.copy_(s)
+    if dist.get_backend() == "nccl":
+        dist.all_reduce(flat, op=dist.ReduceOp.AVG)      # the division rides in the collective
+    else:
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM)
+        flat.div_(world)
+    # one multi-tensor copy instead of one small kernel per parameter
+    torch._foreach_copy_(grads, list(torch._utils._unflatten_dense_tensors(flat, grads)))
 
 
 def hard_ratio(epoch, cfg):
@@ -94,6 +97,8 @@ class AdaptPointTrainer:
             if self.device.type != "cuda":
                 pass                         # torch's SyncBatchNorm has no CPU path (gloo tests): per-rank statistics
             elif self.conv_backend == "tc":    # our BatchNorm kernels all-reduce their (C,2) statistics themselves
+                with torch.cuda.device(self.device):
+                    peer.enable()              # ... over NVLink peer memory when the ranks share a node (peer.py)
                 norm.enable_sync(self.classifier)
                 norm.enable_sync(self.generator)
             else:

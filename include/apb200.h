@@ -204,6 +204,20 @@ int apb_attn_bwd_f32(const float *q, const float *k, const float *v, const float
                      const float *lse, float *dq, float *dk, float *dv, float *delta, int B, int M, int H,
                      int head_dim, apb_stream_t stream);
 
+/* ---- small all-reduce over NVLink peer memory (SyncBN statistics) -------------------------------------------
+ * Replaces the per-layer collective of torch SyncBatchNorm the reference switches on for world_size > 1
+ * (examples/classification/main.py:27, openpoints/models/layers/norm.py:57-71).  Every rank creates one workspace,
+ * the 64-byte CUDA IPC handles are exchanged by the host (torch.distributed), every rank opens its peers' handles,
+ * and apb_peer_allreduce then sums buf[0..n) over the ranks in ONE kernel (P2P stores + flags; CUDA-graph
+ * replayable; n <= apb_peer_max_elems()).  dtype: 0 = f32, 1 = f64.  ws[r] = rank r's workspace as mapped in this
+ * process (ws[rank] = the pointer apb_peer_ws_create returned). */
+int apb_peer_ws_bytes(void);
+int apb_peer_max_elems(void);
+int apb_peer_ws_create(void **ws_out, unsigned char *handle_out64);
+int apb_peer_ws_open(const unsigned char *handle64, void **ws_out);
+int apb_peer_ws_close(void *ws, int own);
+int apb_peer_allreduce(void *buf, int n, int dtype, void *const *ws, int world, int rank, apb_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
