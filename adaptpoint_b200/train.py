@@ -64,12 +64,14 @@ def hard_ratio(epoch, cfg):
     return ap["hardratio_s"] + (ap["hardratio"] - ap["hardratio_s"]) * epoch / cfg["epochs"]
 
 
-def feedback_loss(classifier, criterion, data_real, data_fake, rho):
+def feedback_loss(classifier, criterion, data_real, data_fake, rho, pred_real=None):
     """|1 - exp(L_fake - rho * L_real)| with the classifier in eval mode but inside autograd
-    (ganloss_cls.py:31-65)."""
+    (ganloss_cls.py:31-65).  `pred_real`: logits of the real batch when the caller already has them."""
     classifier.eval()
     pred_fake = classifier(data_fake)
-    if data_real["pos"].requires_grad or data_real["x"].requires_grad or any(p.requires_grad for p in classifier.parameters()):
+    if pred_real is not None:
+        pass
+    elif data_real["pos"].requires_grad or data_real["x"].requires_grad or any(p.requires_grad for p in classifier.parameters()):
         pred_real = classifier(data_real)
     else:   # nothing upstream of the real batch takes a gradient: plain inference (the fused bf16 SA kernels when
         with torch.no_grad():   # the classifier was built with fused=True)
@@ -83,7 +85,7 @@ class AdaptPointTrainer:
     """Holds classifier / imitator / discriminator + their optimizers; `step(batch)` = one train_gan iteration
     followed by one train_one_epoch iteration on the generated batch."""
 
-    def __init__(self, cfg=None, device="cuda", fused_eval=False, seed=0, conv_backend="tc"):
+    def __init__(self, cfg=None, device="cuda", fused_eval=False, seed=0, conv_backend="tc", overlap=True):
         """conv_backend: 'tc' = every 1x1 convolution (fwd, dgrad, wgrad) on the tcgen05 kernels of libapb200
         (bf16/TF32 operands, fp32 accumulation); 'torch' = cuDNN fp32 (strict-parity runs)."""
         self.cfg = copy.deepcopy(ADAPTPOINT_CFG if cfg is None else cfg)
@@ -122,6 +124,13 @@ class AdaptPointTrainer:
         self.epoch = 0
         self._rho = torch.tensor(float(hard_ratio(0, self.cfg)), device=self.device)   # device scalar: graph-safe
         self._graph = None
+        self.overlap = overlap and self.device.type == "cuda"
+        self._side = None
+
+    def _side_stream(self):
+        if self._side is None:
+            self._side = torch.cuda.Stream(device=self.device)
+        return self._side
 
     # -- train_autoaug.py:131-207 ---------------------------------------------------------------------------
     def set_epoch(self, epoch):
@@ -147,21 +156,38 @@ class AdaptPointTrainer:
         points_clone = points.clone()
         inp = points[:, :, :3].contiguous()
         noise = noise or {}
-        self.pointwolf(inp, noise.get("wolf"))                  # the reference runs it for its h5 dump (:143)
         B = inp.size(0)
+        nc = cfg["in_channels"]
+        ratio = cfg.get("feedbackloss_ratio", 1)
+        data_real = {"pos": points_clone[:, :, :3].contiguous(), "y": label,
+                     "x": points_clone[:, :, :nc].transpose(1, 2).contiguous()}
+        # Work that depends on the loader batch only -- PointWOLF (the reference runs it for its h5 dump, :143) and
+        # the classifier's no-grad pass over the REAL batch for the feedback loss -- runs on a side stream beside the
+        # imitator's forward pass (most of whose kernels leave SMs idle at B=32); captured as a parallel graph branch.
+        pred_real, side = None, None
+        if inp.is_cuda and self.overlap:
+            main = torch.cuda.current_stream(inp.device)
+            side = self._side_stream()
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                self.pointwolf(inp, noise.get("wolf"))
+                if ratio > 0:
+                    with torch.no_grad():
+                        pred_real = C(data_real)
+                    pred_real.record_stream(main)
+        else:
+            self.pointwolf(inp, noise.get("wolf"))
         real_label = torch.full((B, 1), 0.9, device=inp.device)
         fake_label = torch.full((B, 1), 0.1, device=inp.device)
 
         _, gen = G(inp, noise.get("gen"))
         g_loss_raw = self.criterion_gan(D(gen), real_label)
         fake_pts = torch.cat([gen, points[:, :, 3:]], dim=-1)   # `points[:, :, :3] = gen_imgs` (:152)
-        nc = cfg["in_channels"]
         data_fake = {"pos": fake_pts[:, :, :3].contiguous(), "y": label,
                      "x": fake_pts[:, :, :nc].transpose(1, 2).contiguous()}
-        data_real = {"pos": points_clone[:, :, :3].contiguous(), "y": label,
-                     "x": points_clone[:, :, :nc].transpose(1, 2).contiguous()}
-        ratio = cfg.get("feedbackloss_ratio", 1)
         g_loss = g_loss_raw
+        if side is not None:
+            torch.cuda.current_stream(inp.device).wait_stream(side)     # join the side branch
         if ratio > 0:
             # The classifier only relays gradients to the imitator here: its own parameter gradients are thrown away by
             # `model_pointcloud.zero_grad()` (train_autoaug.py:232) before they are ever used, so they are not computed.
@@ -169,7 +195,8 @@ class AdaptPointTrainer:
             for p in cparams:
                 p.requires_grad_(False)
             try:
-                g_loss = g_loss_raw + feedback_loss(C, self.criterion, data_real, data_fake, self._rho) * ratio
+                g_loss = g_loss_raw + feedback_loss(C, self.criterion, data_real, data_fake, self._rho,
+                                                    pred_real) * ratio
             finally:
                 for p in cparams:
                     p.requires_grad_(True)
