@@ -1,0 +1,78 @@
+"""Sampling plans: the FPS index chains of one batch of clouds, computed ONCE on a side stream.
+
+Farthest-point sampling depends on coordinates only (subsample.py:76-105 takes xyz and nothing else), so every
+network that walks the same cloud down the same sample counts gets the same indices: in one AdaptPoint iteration the
+imitator (generator_component4_15.py:588-718, reducers 2,2,2,2), the classifier's pass over the real batch
+(ganloss_cls.py:31-65) and PointWOLF / the imitator's anchors (fps to 4 points) all sample the SAME loader batch.
+A `SamplingPlan` runs those chains once, on its own stream, while the feature work of the consumers proceeds; FPS
+launches only 32 CTAs at B=32, so it overlaps with anything.  Consumers call `sample(p, m)`, which returns the
+plan's indices when `p` is tagged as a node of a plan holding fps(p, m), and otherwise just runs FPS.
+
+Tags are Python attributes on the tensor objects (`p._apb_plan = (plan, path, version)`): the plan's root is tagged
+by its creator, and every `new_p` that `sample` gathers is tagged with the path below it.
+"""
+import torch
+
+from . import ops
+
+
+class SamplingPlan:
+    def __init__(self, root, chains, stream=None):
+        """root (B,N,3) f32 contiguous CUDA tensor; chains e.g. [[1024, 512, 256, 128], [4]]: fps(root,1024),
+        fps(root[idx],512), ... and fps(root,4).  Work is enqueued on `stream` (after what the current stream has
+        enqueued so far), one event per node."""
+        self.nodes = {}                       # path tuple -> (idx int64 (B,m), event)
+        self.stream = stream
+        cur = torch.cuda.current_stream(root.device)
+        base = root.detach()
+        if stream is not None:
+            stream.wait_stream(cur)
+            base.record_stream(stream)
+        with torch.cuda.stream(stream if stream is not None else cur):
+            for chain in chains:
+                xyz, path = base, ()
+                for k, m in enumerate(chain):
+                    path = path + (int(m),)
+                    if path in self.nodes:    # shared prefix of two chains
+                        idx = self.nodes[path][0]
+                    else:
+                        idx = ops.furthest_point_sample(xyz, int(m)).long()
+                        ev = torch.cuda.Event()
+                        ev.record()
+                        self.nodes[path] = (idx, ev)
+                    if k + 1 < len(chain):
+                        xyz = torch.gather(xyz, 1, idx.unsqueeze(-1).expand(-1, -1, 3))
+        self.adopt(root)
+
+    def adopt(self, tensor, path=()):
+        """Declare that `tensor` holds the coordinates of node `path` (the root by default)."""
+        tensor._apb_plan = (self, tuple(path), tensor._version)
+        return tensor
+
+    def lookup(self, p, m):
+        tag = getattr(p, "_apb_plan", None)
+        if tag is None or tag[0] is not self or tag[2] != p._version:
+            return None
+        return self.nodes.get(tag[1] + (int(m),)), tag[1] + (int(m),)
+
+
+def sample(p, m):
+    """(idx int64 (B,m), new_p (B,m,3)) = FPS of p (B,N,3) to m points; new_p is gathered from `p` on the current
+    stream (so it stays inside autograd).  Uses the plan `p` is tagged with when it holds this node."""
+    tag = getattr(p, "_apb_plan", None)
+    idx = None
+    if tag is not None and p.is_cuda:
+        plan = tag[0]
+        hit = plan.lookup(p, m)
+        if hit is not None and hit[0] is not None:
+            (idx, ev), path = hit
+            cur = torch.cuda.current_stream(p.device)
+            cur.wait_event(ev)
+            idx.record_stream(cur)
+    if idx is None:
+        idx = ops.furthest_point_sample(p.contiguous(), int(m)).long()
+        path = None
+    new_p = torch.gather(p, 1, idx.unsqueeze(-1).expand(-1, -1, 3))
+    if path is not None:
+        tag[0].adopt(new_p, path)
+    return idx, new_p

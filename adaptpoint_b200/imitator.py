@@ -23,7 +23,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 from torch.autograd import Function
 
-from . import _cabi, ops
+from . import _cabi, geometry, ops
 from .norm import ConvBlock, TcBatchNorm1d
 from .tcconv import TcConv1d, TcConv2d, conv_max
 
@@ -125,8 +125,7 @@ class PointWOLF_classversion(object):
         B, N, _ = xyz.shape
         dev = xyz.device
         noise = self.draw(B) if noise is None else noise
-        fps_idx = ops.furthest_point_sample(xyz.contiguous(), self.num_anchor).long()
-        anchor = _index_points(xyz, fps_idx)
+        fps_idx, anchor = geometry.sample(xyz, self.num_anchor)
         drop, axis = noise["dropout"].to(dev), noise["axis"].to(dev).float()
         degree = math.pi * noise["R"].to(dev) / 180.0 * drop[:, :, 0:1]
         scale = noise["S"].to(dev) * drop[:, :, 1:2] * axis
@@ -184,8 +183,7 @@ class PointsetGrouper(nn.Module):
         """xyz (B,N,3), feats (B,C,N) -> new_xyz (B,np,3), new_feats (B,C,np)."""
         xyz = xyz.contiguous()
         B, C, N = feats.shape
-        fps_idx = ops.furthest_point_sample(xyz, N // self.reduce).long()
-        new_xyz = torch.gather(xyz, 1, fps_idx.unsqueeze(-1).expand(-1, -1, 3))
+        fps_idx, new_xyz = geometry.sample(xyz, N // self.reduce)          # shared FPS chain when xyz belongs to a plan
         centre = torch.gather(feats, 2, fps_idx.unsqueeze(1).expand(-1, C, -1))            # (B,C,np)
         idx = ops.ball_query(self.radi, self.kneighbors, xyz, new_xyz)
         if self.normalize == "center":   # needs the mean over the neighbours: unfused composition
@@ -338,8 +336,7 @@ class AdaptPoint_Augmentor(nn.Module):
         """xyz (B,N,3) -> (xyz, xyz_new).  noise: optional dict(dropout, axis, proj_axis[, gumbel])."""
         B, N, _ = xyz.shape
         dev = xyz.device
-        fps_idx = ops.furthest_point_sample(xyz.contiguous(), self.num_anchor).long()
-        anchor = _index_points(xyz, fps_idx)
+        fps_idx, anchor = geometry.sample(xyz, self.num_anchor)
         probs, masking = self.predict_prob_layer(xyz, fps_idx, None if noise is None else noise.get("gumbel"))
         noise = self.draw(B) if noise is None else noise
         drop, axis = noise["dropout"].to(dev), noise["axis"].to(dev).float()

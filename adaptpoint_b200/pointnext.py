@@ -18,7 +18,7 @@ from typing import List
 import torch
 import torch.nn as nn
 
-from . import ops
+from . import geometry, ops
 from .norm import ConvBlock, bn_max
 from .layers import (CHANNEL_MAP, create_act, create_convblock1d, create_convblock2d, create_grouper,
                      get_aggregation_feautres, QueryAndGroup)
@@ -146,8 +146,11 @@ class SetAbstraction(nn.Module):
         if self.all_aggr:
             dp, fj = self.grouper(p, p, f)
             return p, _convs_pool(self, get_aggregation_feautres(p, dp, None, fj, self.feature_type))
-        idx = self.sample_fn(p, p.shape[1] // self.stride).long()
-        new_p = torch.gather(p, 1, idx.unsqueeze(-1).expand(-1, -1, 3))
+        if self.sample_fn is ops.furthest_point_sample:
+            idx, new_p = geometry.sample(p, p.shape[1] // self.stride)       # shared FPS chain when p belongs to a plan
+        else:
+            idx = self.sample_fn(p, p.shape[1] // self.stride).long()
+            new_p = torch.gather(p, 1, idx.unsqueeze(-1).expand(-1, -1, 3))
         fi = identity = None
         if self.use_res or "df" in self.feature_type:
             fi = torch.gather(f, -1, idx.unsqueeze(1).expand(-1, f.shape[1], -1))

@@ -21,7 +21,7 @@ import torch
 import torch.distributed as dist
 import torch.nn as nn
 
-from . import norm, ops, peer, tcconv
+from . import geometry, norm, ops, peer, tcconv
 from .imitator import AdaptPoint_Augmentor, PointDiscriminator1, PointWOLF_classversion
 from .models import SmoothCrossEntropy, build_model
 
@@ -126,11 +126,40 @@ class AdaptPointTrainer:
         self._graph = None
         self.overlap = overlap and self.device.type == "cuda"
         self._side = None
+        self._geo = None
+        self._prepared = None
 
     def _side_stream(self):
         if self._side is None:
             self._side = torch.cuda.Stream(device=self.device)
         return self._side
+
+    def _geo_stream(self):
+        if self._geo is None:
+            self._geo = torch.cuda.Stream(device=self.device)
+        return self._geo
+
+    def _cls_chain(self, n):
+        """Sample counts of the classifier's FPS chain on an n-point cloud (one per strided stage)."""
+        chain = []
+        for s in getattr(self.classifier.encoder, "strides", []):
+            if s > 1:
+                n = n // s
+                chain.append(n)
+        return chain
+
+    def _gen_chain(self, n):
+        chain = []
+        for g in self.generator.predict_prob_layer.pointset_grouper_list:
+            n = n // g.reduce
+            chain.append(n)
+        return chain
+
+    def _resample_count(self, n_loader_points):
+        npoints = self.cfg["num_points"]
+        if n_loader_points <= npoints:
+            return None
+        return min({1024: 1200, 4096: 4800, 8192: 8192}[npoints], n_loader_points)
 
     # -- train_autoaug.py:131-207 ---------------------------------------------------------------------------
     def set_epoch(self, epoch):
@@ -159,8 +188,14 @@ class AdaptPointTrainer:
         B = inp.size(0)
         nc = cfg["in_channels"]
         ratio = cfg.get("feedbackloss_ratio", 1)
-        data_real = {"pos": points_clone[:, :, :3].contiguous(), "y": label,
-                     "x": points_clone[:, :, :nc].transpose(1, 2).contiguous()}
+        # nothing below writes into `points`, so the real batch's coordinates ARE `inp` (the reference clones because
+        # it overwrites points[:, :, :3] with the generated cloud, :152)
+        data_real = {"pos": inp, "y": label, "x": points_clone[:, :, :nc].transpose(1, 2).contiguous()}
+        N = inp.shape[1]
+        if inp.is_cuda and self.overlap:
+            # one FPS chain for everything that samples the loader batch: imitator, classifier(real), both anchor sets
+            geometry.SamplingPlan(inp, [self._gen_chain(N), self._cls_chain(N), [G.num_anchor],
+                                        [self.pointwolf.num_anchor]], self._geo_stream())
         # Work that depends on the loader batch only -- PointWOLF (the reference runs it for its h5 dump, :143) and
         # the classifier's no-grad pass over the REAL batch for the feedback loss -- runs on a side stream beside the
         # imitator's forward pass (most of whose kernels leave SMs idle at B=32); captured as a parallel graph branch.
@@ -185,6 +220,19 @@ class AdaptPointTrainer:
         fake_pts = torch.cat([gen, points[:, :, 3:]], dim=-1)   # `points[:, :, :3] = gen_imgs` (:152)
         data_fake = {"pos": fake_pts[:, :, :3].contiguous(), "y": label,
                      "x": fake_pts[:, :, :nc].transpose(1, 2).contiguous()}
+        self._prepared = None
+        fake_det = fake_pts.detach()
+        if inp.is_cuda and self.overlap:
+            # geometry of the generated cloud (classifier(fake) chain + the resampling FPS) and the whole classifier
+            # batch of the next iteration (resample, gather, its FPS chain) on the geometry stream, beside the
+            # feedback loss and the two backward passes
+            geo = self._geo_stream()
+            point_all = self._resample_count(N)
+            plan = geometry.SamplingPlan(data_fake["pos"], [self._cls_chain(N)] + ([[point_all]] if point_all else []),
+                                         geo)
+            if point_all:
+                with torch.cuda.stream(geo):
+                    self._prepared = self._resample(fake_det, plan.nodes[(point_all,)][0], noise.get("keep"))
         g_loss = g_loss_raw
         if side is not None:
             torch.cuda.current_stream(inp.device).wait_stream(side)     # join the side branch
@@ -213,7 +261,20 @@ class AdaptPointTrainer:
         allreduce_grads(list(D.parameters()))
         self.opt_d.step()
         C.zero_grad(set_to_none=True)                           # model_pointcloud.zero_grad() (:232)
-        return fake_pts.detach(), g_loss.detach(), d_loss.detach()
+        return fake_det, g_loss.detach(), d_loss.detach()
+
+    def _resample(self, points, fps_idx, keep=None):
+        """Point resampling strategy (train_autoaug.py:485-499): a random npoints-subset of the FPS sample.  Runs on
+        the current stream; on CUDA it also starts the classifier's FPS chain on the resampled cloud."""
+        npoints = self.cfg["num_points"]
+        if keep is None:                                        # np.random.choice(point_all, npoints, False)
+            keep = torch.randperm(fps_idx.shape[1])[:npoints]
+        fps_idx = fps_idx[:, keep.to(points.device)]
+        out = torch.gather(points, 1, fps_idx.unsqueeze(-1).expand(-1, -1, points.shape[-1]))
+        pos = out[:, :, :3].contiguous()
+        if pos.is_cuda and self.overlap:
+            geometry.SamplingPlan(pos, [self._cls_chain(npoints)], None)
+        return {"source": points, "points": out, "pos": pos}
 
     # -- train_autoaug.py:474-506 ---------------------------------------------------------------------------
     def classifier_iteration(self, points, target, keep=None):
@@ -221,17 +282,20 @@ class AdaptPointTrainer:
         model = self.classifier
         model.train()
         npoints = cfg["num_points"]
-        if points.shape[1] > npoints:                           # point resampling strategy (:485-499)
-            point_all = {1024: 1200, 4096: 4800, 8192: 8192}[npoints]
-            point_all = min(point_all, points.size(1))
-            fps_idx = ops.furthest_point_sample(points[:, :, :3].contiguous(), point_all)
-            if keep is None:                                    # np.random.choice(point_all, npoints, False)
-                keep = torch.randperm(point_all)[:npoints]
-            keep = keep.to(points.device)
-            fps_idx = fps_idx[:, keep]
-            points = torch.gather(points, 1, fps_idx.unsqueeze(-1).long().expand(-1, -1, points.shape[-1]))
-        data = {"pos": points[:, :, :3].contiguous(),
-                "x": points[:, :, :cfg["in_channels"]].transpose(1, 2).contiguous()}
+        prepared, self._prepared = self._prepared, None
+        if prepared is not None and prepared["source"] is points:      # resampled on the geometry stream already
+            main = torch.cuda.current_stream(points.device)
+            main.wait_stream(self._geo_stream())
+            points, pos = prepared["points"], prepared["pos"]
+            points.record_stream(main)
+            pos.record_stream(main)
+        else:
+            if points.shape[1] > npoints:                       # point resampling strategy (:485-499)
+                point_all = self._resample_count(points.size(1))
+                fps_idx = ops.furthest_point_sample(points[:, :, :3].contiguous(), point_all).long()
+                points = self._resample(points, fps_idx, keep)["points"]
+            pos = points[:, :, :3].contiguous()
+        data = {"pos": pos, "x": points[:, :, :cfg["in_channels"]].transpose(1, 2).contiguous()}
         logits, loss = model.get_logits_loss(data, target)
         loss.backward()
         allreduce_grads(list(model.parameters()))
@@ -245,6 +309,10 @@ class AdaptPointTrainer:
         with tcconv.conv_backend(self.conv_backend):
             fake, g_loss, d_loss = self.gan_iteration(points, label, noise)
             _, loss = self.classifier_iteration(fake, label, noise.get("keep"))
+            if self.overlap:     # every branch rejoins the main stream before the step ends (graph capture needs it)
+                main = torch.cuda.current_stream(self.device)
+                main.wait_stream(self._geo_stream())
+                main.wait_stream(self._side_stream())
         return loss, g_loss, d_loss
 
     def step(self, points, label):

@@ -44,3 +44,48 @@ def test_graph_step_trains(cuda_dev, conv):
     torch.cuda.synchronize()
     moved = sum(float((a - b.detach()).abs().sum()) for a, b in zip(p0, tr.classifier.parameters()))
     assert moved > 0
+
+
+def test_overlap_branches_match_serial_step(cuda_dev):
+    """Side-stream branches + shared sampling plans (train.py, geometry.py) only reorder independent work: the first
+    two eager steps give the same three losses as the serial launch order (fp32 atomics: 1e-4)."""
+    from adaptpoint_b200.synth import make_clouds
+    from adaptpoint_b200.train import AdaptPointTrainer
+    pos = make_clouds(8, 2048, "shell", 5)
+    pts = torch.cat([pos, pos[:, :, 1:2] - pos[:, :, 1:2].amin(1, keepdim=True)], -1).to(cuda_dev)
+    y = (torch.arange(8) % 15).to(cuda_dev)
+    got = []
+    for overlap in (False, True):
+        torch.manual_seed(0)
+        torch.cuda.manual_seed(0)
+        tr = AdaptPointTrainer(device=cuda_dev, seed=0, conv_backend="torch", overlap=overlap)
+        torch.manual_seed(1)
+        torch.cuda.manual_seed(1)
+        rows = []
+        for _ in range(2):
+            rows.append(torch.stack([o.float() for o in tr.step(pts.clone(), y)]).cpu())
+        got.append(torch.stack(rows))
+    assert torch.isfinite(got[0]).all()
+    assert torch.allclose(got[0], got[1], rtol=1e-4, atol=1e-4), (got[0], got[1])
+
+
+def test_sampling_plan_equals_direct_fps(cuda_dev):
+    from adaptpoint_b200 import geometry, ops
+    from adaptpoint_b200.synth import make_clouds
+    xyz = make_clouds(4, 2048, "ball", 3).to(cuda_dev)
+    side = torch.cuda.Stream(device=cuda_dev)
+    geometry.SamplingPlan(xyz, [[1024, 512, 256], [4], [1024, 300]], side)
+    p = xyz
+    for m in (1024, 512, 256):
+        want = ops.furthest_point_sample(p.contiguous(), m).long()
+        idx, new_p = geometry.sample(p, m)
+        assert hasattr(new_p, "_apb_plan") and torch.equal(idx, want)
+        p = new_p
+    idx4, _ = geometry.sample(xyz, 4)
+    assert torch.equal(idx4, ops.furthest_point_sample(xyz, 4).long())
+    idx7, new7 = geometry.sample(xyz, 7)                     # not in the plan: plain FPS, untagged
+    assert torch.equal(idx7, ops.furthest_point_sample(xyz, 7).long()) and not hasattr(new7, "_apb_plan")
+    xyz.add_(0.0)                                            # in-place write invalidates the tag (version bump)
+    idx, new_p = geometry.sample(xyz, 1024)
+    assert not hasattr(new_p, "_apb_plan")
+    torch.cuda.synchronize()
