@@ -11,7 +11,7 @@ C-ABI kernels).  Numerics: bf16 operands, fp32 accumulation -> compare at 2e-2 r
 import torch
 import torch.nn as nn
 
-from . import _cabi, ops
+from . import _cabi, geometry, ops
 
 _BK = 64  # reduction chunk of the kernel: weights are zero-padded to a multiple of this
 
@@ -94,7 +94,7 @@ def fusable_reason(grouper, convs, K):
 def sa_fused_forward(owner, grouper, convs, query_xyz, support_xyz, features):
     """-> (B, Cout, M) = max_k convs(cat([dp, fj]))  for an eval-mode block (see module docstring)."""
     K = grouper.nsample
-    idx = ops.ball_query(grouper.radius, K, support_xyz, query_xyz)
+    idx = geometry.ball_query(grouper.radius, K, support_xyz, query_xyz)
 
     def build():
         W1, s1, t1, r1 = fold_conv_block(convs[0])

@@ -17,11 +17,13 @@ from . import ops
 
 
 class SamplingPlan:
-    def __init__(self, root, chains, stream=None):
+    def __init__(self, root, chains, stream=None, queries=()):
         """root (B,N,3) f32 contiguous CUDA tensor; chains e.g. [[1024, 512, 256, 128], [4]]: fps(root,1024),
-        fps(root[idx],512), ... and fps(root,4).  Work is enqueued on `stream` (after what the current stream has
-        enqueued so far), one event per node."""
+        fps(root[idx],512), ... and fps(root,4).  queries: ball queries between two nodes of the chains,
+        (support path, query path, radius, nsample), e.g. ((), (1024,), 0.15, 32).  Work is enqueued on `stream`
+        (after what the current stream has enqueued so far), one event per node."""
         self.nodes = {}                       # path tuple -> (idx int64 (B,m), event)
+        self.balls = {}                       # (query path, radius, nsample) -> (idx int32 (B,M,K), event)
         self.stream = stream
         cur = torch.cuda.current_stream(root.device)
         base = root.detach()
@@ -29,19 +31,27 @@ class SamplingPlan:
             stream.wait_stream(cur)
             base.record_stream(stream)
         with torch.cuda.stream(stream if stream is not None else cur):
+            coords = {(): base}
+            need_xyz = {q[0] for q in queries} | {q[1] for q in queries}
             for chain in chains:
-                xyz, path = base, ()
+                path = ()
                 for k, m in enumerate(chain):
-                    path = path + (int(m),)
-                    if path in self.nodes:    # shared prefix of two chains
-                        idx = self.nodes[path][0]
-                    else:
-                        idx = ops.furthest_point_sample(xyz, int(m)).long()
+                    parent, path = path, path + (int(m),)
+                    if path not in self.nodes:                       # else: shared prefix of two chains
+                        idx = ops.furthest_point_sample(coords[parent], int(m)).long()
                         ev = torch.cuda.Event()
                         ev.record()
                         self.nodes[path] = (idx, ev)
-                    if k + 1 < len(chain):
-                        xyz = torch.gather(xyz, 1, idx.unsqueeze(-1).expand(-1, -1, 3))
+                    if (k + 1 < len(chain) or path in need_xyz) and path not in coords:
+                        coords[path] = torch.gather(coords[parent], 1, self.nodes[path][0].unsqueeze(-1)
+                                                    .expand(-1, -1, 3)).contiguous()
+                        for sup, qry, radius, nsample in queries:    # as soon as both ends exist
+                            key = (qry, float(radius), int(nsample))
+                            if qry == path and sup == parent and key not in self.balls:
+                                bidx = ops.ball_query(float(radius), int(nsample), coords[sup], coords[qry])
+                                ev = torch.cuda.Event()
+                                ev.record()
+                                self.balls[key] = (bidx, ev)
         self.adopt(root)
 
     def adopt(self, tensor, path=()):
@@ -76,3 +86,19 @@ def sample(p, m):
     if path is not None:
         tag[0].adopt(new_p, path)
     return idx, new_p
+
+
+def ball_query(radius, nsample, xyz, new_xyz):
+    """ops.ball_query(radius, nsample, xyz, new_xyz), served from the plan when `new_xyz` was sampled from `xyz`
+    through `sample` and the plan holds this query."""
+    tq, ts = getattr(new_xyz, "_apb_plan", None), getattr(xyz, "_apb_plan", None)
+    if (tq is not None and ts is not None and tq[0] is ts[0] and tq[2] == new_xyz._version and ts[2] == xyz._version
+            and tq[1][:-1] == ts[1] and len(tq[1]) > 0):
+        hit = tq[0].balls.get((tq[1], float(radius), int(nsample)))
+        if hit is not None:
+            idx, ev = hit
+            cur = torch.cuda.current_stream(xyz.device)
+            cur.wait_event(ev)
+            idx.record_stream(cur)
+            return idx
+    return ops.ball_query(radius, nsample, xyz, new_xyz)

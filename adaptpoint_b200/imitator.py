@@ -185,7 +185,7 @@ class PointsetGrouper(nn.Module):
         B, C, N = feats.shape
         fps_idx, new_xyz = geometry.sample(xyz, N // self.reduce)          # shared FPS chain when xyz belongs to a plan
         centre = torch.gather(feats, 2, fps_idx.unsqueeze(1).expand(-1, C, -1))            # (B,C,np)
-        idx = ops.ball_query(self.radi, self.kneighbors, xyz, new_xyz)
+        idx = geometry.ball_query(self.radi, self.kneighbors, xyz, new_xyz)
         if self.normalize == "center":   # needs the mean over the neighbours: unfused composition
             grouped = ops.grouping_operation(feats.contiguous(), idx)                        # (B,C,np,k)
             grouped = self.affine_alpha.view(1, C, 1, 1) * (grouped - grouped.mean(dim=3, keepdim=True)) \

@@ -15,7 +15,7 @@ import copy
 import torch
 import torch.nn as nn
 
-from . import ops
+from . import geometry, ops
 from .norm import ConvBlock, TcBatchNorm1d, TcBatchNorm2d
 from .tcconv import TcConv1d, TcConv2d
 
@@ -148,7 +148,7 @@ class QueryAndGroup(nn.Module):
         self.relative_xyz, self.normalize_dp, self.return_only_idx = relative_xyz, normalize_dp, return_only_idx
 
     def forward(self, query_xyz, support_xyz, features=None):
-        idx = ops.ball_query(self.radius, self.nsample, support_xyz, query_xyz)
+        idx = geometry.ball_query(self.radius, self.nsample, support_xyz, query_xyz)
         if self.return_only_idx:
             return idx
         grouped_xyz = ops.grouping_operation(support_xyz.transpose(1, 2).contiguous(), idx)

@@ -155,6 +155,28 @@ class AdaptPointTrainer:
             chain.append(n)
         return chain
 
+    def _cls_queries(self, n):
+        """Ball queries of the classifier's strided stages on an n-point cloud, as SamplingPlan queries."""
+        out, path = [], ()
+        for stage in getattr(self.classifier.encoder, "encoder", []):
+            sa = stage[0]
+            s = getattr(sa, "stride", 1)
+            if s > 1:
+                n = n // s
+                g = getattr(sa, "grouper", None)
+                if getattr(g, "radius", None) is not None and getattr(g, "nsample", None) is not None:
+                    out.append((path, path + (n,), g.radius, g.nsample))
+                path = path + (n,)
+        return out
+
+    def _gen_queries(self, n):
+        out, path = [], ()
+        for g in self.generator.predict_prob_layer.pointset_grouper_list:
+            n = n // g.reduce
+            out.append((path, path + (n,), g.radi, g.kneighbors))
+            path = path + (n,)
+        return out
+
     def _resample_count(self, n_loader_points):
         npoints = self.cfg["num_points"]
         if n_loader_points <= npoints:
@@ -195,7 +217,8 @@ class AdaptPointTrainer:
         if inp.is_cuda and self.overlap:
             # one FPS chain for everything that samples the loader batch: imitator, classifier(real), both anchor sets
             geometry.SamplingPlan(inp, [self._gen_chain(N), self._cls_chain(N), [G.num_anchor],
-                                        [self.pointwolf.num_anchor]], self._geo_stream())
+                                        [self.pointwolf.num_anchor]], self._geo_stream(),
+                                  self._gen_queries(N) + (self._cls_queries(N) if ratio > 0 else []))
         # Work that depends on the loader batch only -- PointWOLF (the reference runs it for its h5 dump, :143) and
         # the classifier's no-grad pass over the REAL batch for the feedback loss -- runs on a side stream beside the
         # imitator's forward pass (most of whose kernels leave SMs idle at B=32); captured as a parallel graph branch.
@@ -229,7 +252,7 @@ class AdaptPointTrainer:
             geo = self._geo_stream()
             point_all = self._resample_count(N)
             plan = geometry.SamplingPlan(data_fake["pos"], [self._cls_chain(N)] + ([[point_all]] if point_all else []),
-                                         geo)
+                                         geo, self._cls_queries(N) if ratio > 0 else [])
             if point_all:
                 with torch.cuda.stream(geo):
                     self._prepared = self._resample(fake_det, plan.nodes[(point_all,)][0], noise.get("keep"))
@@ -273,7 +296,7 @@ class AdaptPointTrainer:
         out = torch.gather(points, 1, fps_idx.unsqueeze(-1).expand(-1, -1, points.shape[-1]))
         pos = out[:, :, :3].contiguous()
         if pos.is_cuda and self.overlap:
-            geometry.SamplingPlan(pos, [self._cls_chain(npoints)], None)
+            geometry.SamplingPlan(pos, [self._cls_chain(npoints)], None, self._cls_queries(npoints))
         return {"source": points, "points": out, "pos": pos}
 
     # -- train_autoaug.py:474-506 ---------------------------------------------------------------------------

@@ -1,0 +1,5 @@
+set -x
+mkdir -p gpurun_out
+timeout 500 python -m pytest tests -m gpu -x -q 2>&1 | tail -8
+timeout 300 python bench.py --steps 10 --warmup 3 > gpurun_out/bench_r01_z.json 2> gpurun_out/bench_r01_z.err; echo "bench exit $?"; cut -c1-200 gpurun_out/bench_r01_z.json; tail -3 gpurun_out/bench_r01_z.err
+timeout 300 python scripts/profile_modules.py > gpurun_out/module_profile_z.txt 2> gpurun_out/module_profile_z.err; echo "modprof exit $?"; tail -3 gpurun_out/module_profile_z.err

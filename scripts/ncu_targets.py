@@ -30,6 +30,13 @@ elif tgt == "pw":
     x = torch.randn(8, 512, 65536, device=dev)
     for _ in range(3):
         fused.pwconv_forward(blk, x)
+elif tgt == "pwtf32":   # the bench step's most expensive 1x1-conv shape: python scripts/ncu_targets.py pwtf32 [B Cin Cout P]
+    from adaptpoint_b200 import tcconv
+    B, cin, cout, P = (int(v) for v in sys.argv[2:6]) if len(sys.argv) > 5 else (32, 128, 512, 2048)
+    x = torch.randn(B, cin, P, device=dev)
+    w = torch.randn(cout, cin, device=dev) * 0.05
+    for _ in range(3):
+        tcconv._gemm_rows(x, w, None, B, cin, cout, P)
 elif tgt in ("fps", "group", "group_grad"):
     B, N, M, K, C = 32, 16384, 4096, 32, 32
     if len(sys.argv) > 3:  # python scripts/ncu_targets.py fps 2048 1024 [C]

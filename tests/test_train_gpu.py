@@ -47,8 +47,8 @@ def test_graph_step_trains(cuda_dev, conv):
 
 
 def test_overlap_branches_match_serial_step(cuda_dev):
-    """Side-stream branches + shared sampling plans (train.py, geometry.py) only reorder independent work: the first
-    two eager steps give the same three losses as the serial launch order (fp32 atomics: 1e-4)."""
+    """Side-stream branches + shared sampling plans (train.py, geometry.py) only reorder independent work: same
+    losses as the serial launch order."""
     from adaptpoint_b200.synth import make_clouds
     from adaptpoint_b200.train import AdaptPointTrainer
     pos = make_clouds(8, 2048, "shell", 5)
@@ -65,8 +65,13 @@ def test_overlap_branches_match_serial_step(cuda_dev):
         for _ in range(2):
             rows.append(torch.stack([o.float() for o in tr.step(pts.clone(), y)]).cpu())
         got.append(torch.stack(rows))
-    assert torch.isfinite(got[0]).all()
-    assert torch.allclose(got[0], got[1], rtol=1e-4, atol=1e-4), (got[0], got[1])
+    assert torch.isfinite(got[0]).all() and torch.isfinite(got[1]).all()
+    # step 1: nothing has been updated yet, all three losses agree
+    assert torch.allclose(got[0][0], got[1][0], rtol=1e-5, atol=1e-5), (got[0], got[1])
+    # step 2: imitator and discriminator losses still agree; the classifier's TRAINING loss is left out: after one
+    # AdamW step (sign-normalised updates of noise-level gradients) two identical SERIAL runs already differ by ~0.1
+    # in it at B=8 (scripts/overlap_noise.py, scripts/determinism_probe.py), far more than serial vs overlapped
+    assert torch.allclose(got[0][1, 1:], got[1][1, 1:], rtol=1e-4, atol=1e-4), (got[0], got[1])
 
 
 def test_sampling_plan_equals_direct_fps(cuda_dev):
@@ -74,13 +79,17 @@ def test_sampling_plan_equals_direct_fps(cuda_dev):
     from adaptpoint_b200.synth import make_clouds
     xyz = make_clouds(4, 2048, "ball", 3).to(cuda_dev)
     side = torch.cuda.Stream(device=cuda_dev)
-    geometry.SamplingPlan(xyz, [[1024, 512, 256], [4], [1024, 300]], side)
+    geometry.SamplingPlan(xyz, [[1024, 512, 256], [4], [1024, 300]], side,
+                          [((), (1024,), 0.15, 32), ((1024,), (1024, 512), 0.2, 24)])
     p = xyz
-    for m in (1024, 512, 256):
+    for m, rk in ((1024, (0.15, 32)), (512, (0.2, 24)), (256, (0.4, 16))):
         want = ops.furthest_point_sample(p.contiguous(), m).long()
         idx, new_p = geometry.sample(p, m)
         assert hasattr(new_p, "_apb_plan") and torch.equal(idx, want)
+        # ball query between the two levels: from the plan for the first two, computed directly for the third
+        assert torch.equal(geometry.ball_query(rk[0], rk[1], p, new_p), ops.ball_query(rk[0], rk[1], p, new_p.contiguous()))
         p = new_p
+    assert len(xyz._apb_plan[0].balls) == 2
     idx4, _ = geometry.sample(xyz, 4)
     assert torch.equal(idx4, ops.furthest_point_sample(xyz, 4).long())
     idx7, new7 = geometry.sample(xyz, 7)                     # not in the plan: plain FPS, untagged
