@@ -359,6 +359,8 @@ def run_ours(args):
                                     + ("; no-grad classifier pass of the feedback loss: fused bf16 SA kernels (2e-2)"
                                        if args.fused_eval else ""),
                        "cuda_graph": bool(args.graph),
+                       "schedule": "loader-only work (PointWOLF, no-grad classifier pass on the real batch) and all FPS / "
+                                   "ball-query chains run as parallel branches of the graph (train.py, geometry.py)",
                        "kernel_trace": f"C-ABI launches timed with CUDA events over {trace_steps} eager steps before "
                                        "the timed region (same kernels the graph replays), scaled to K steps",
                        "l2": "256 MB flush write between timed steps (outside the per-step event pairs)",
