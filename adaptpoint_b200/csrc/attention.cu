@@ -26,34 +26,110 @@ __device__ __forceinline__ float ex2(float x) {
     return y;
 }
 
-__device__ __forceinline__ void load_row(const float *p, float (&r)[D]) {
+// Packed fp32 pairs: on sm_100 a three-register FFMA issues every other cycle per scheduler (register-port bound), an
+// FFMA2 (fma.rn.f32x2, two independent fp32 FMAs on a 64-bit register pair) issues at the same rate, so the fp32 FMA
+// peak is only reachable through FFMA2.  A 16-float row is held as 8 pairs; results are ordinary IEEE fp32 FMAs.
+typedef unsigned long long f2;
+constexpr int D2 = D / 2;
+__device__ __forceinline__ f2 pk(float lo, float hi) {
+    f2 r;
+    asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ float hsum(f2 a) {
+    float lo, hi;
+    asm("mov.b64 {%0,%1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a));
+    return lo + hi;
+}
+__device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) {
+    f2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ f2 mul2(f2 a, f2 b) {
+    f2 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f2 add2(f2 a, f2 b) {
+    f2 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+
+__device__ __forceinline__ void load_row(const float *p, f2 (&r)[D2]) {
 #pragma unroll
-    for (int c = 0; c < D; c += 4) {
-        const float4 t = __ldg(reinterpret_cast<const float4 *>(p + c));
-        r[c] = t.x; r[c + 1] = t.y; r[c + 2] = t.z; r[c + 3] = t.w;
+    for (int c = 0; c < D2; c += 2) {
+        const float4 t = __ldg(reinterpret_cast<const float4 *>(p + 2 * c));
+        r[c] = pk(t.x, t.y);
+        r[c + 1] = pk(t.z, t.w);
     }
 }
-__device__ __forceinline__ void store_row(float *p, const float (&r)[D]) {
+__device__ __forceinline__ void store_row(float *p, const f2 (&r)[D2]) {
 #pragma unroll
-    for (int c = 0; c < D; c += 4) *reinterpret_cast<float4 *>(p + c) = make_float4(r[c], r[c + 1], r[c + 2], r[c + 3]);
-}
-__device__ __forceinline__ float dot_smem(const float (&a)[D], const float *s) {
-    float acc = 0.f;
-#pragma unroll
-    for (int c = 0; c < D; c += 4) {
-        const float4 t = *reinterpret_cast<const float4 *>(s + c);
-        acc = fmaf(a[c], t.x, acc); acc = fmaf(a[c + 1], t.y, acc);
-        acc = fmaf(a[c + 2], t.z, acc); acc = fmaf(a[c + 3], t.w, acc);
+    for (int c = 0; c < D2; c += 2) {
+        ulonglong2 t;
+        t.x = r[c];
+        t.y = r[c + 1];
+        *reinterpret_cast<ulonglong2 *>(p + 2 * c) = t;
     }
-    return acc;
 }
-__device__ __forceinline__ void axpy_smem(float (&acc)[D], float a, const float *s) {
+__device__ __forceinline__ void scale_row(f2 (&r)[D2], float a) {
+    const f2 a2 = pk(a, a);
 #pragma unroll
-    for (int c = 0; c < D; c += 4) {
-        const float4 t = *reinterpret_cast<const float4 *>(s + c);
-        acc[c] = fmaf(a, t.x, acc[c]); acc[c + 1] = fmaf(a, t.y, acc[c + 1]);
-        acc[c + 2] = fmaf(a, t.z, acc[c + 2]); acc[c + 3] = fmaf(a, t.w, acc[c + 3]);
+    for (int c = 0; c < D2; ++c) r[c] = mul2(r[c], a2);
+}
+__device__ __forceinline__ void zero_row(f2 (&r)[D2]) {
+#pragma unroll
+    for (int c = 0; c < D2; ++c) r[c] = 0ull;
+}
+// a . s  (s: 16 floats in shared memory, 16-byte aligned): two chains of 4 FFMA2
+__device__ __forceinline__ float dot_smem(const f2 (&a)[D2], const float *s) {
+    const ulonglong2 *s2 = reinterpret_cast<const ulonglong2 *>(s);
+    ulonglong2 t = s2[0];
+    f2 e = mul2(a[0], t.x), o = mul2(a[1], t.y);
+#pragma unroll
+    for (int c = 1; c < D2 / 2; ++c) {
+        t = s2[c];
+        e = fma2(a[2 * c], t.x, e);
+        o = fma2(a[2 * c + 1], t.y, o);
     }
+    return hsum(add2(e, o));
+}
+__device__ __forceinline__ float dot_reg(const f2 (&a)[D2], const f2 (&b)[D2]) {
+    f2 e = mul2(a[0], b[0]), o = mul2(a[1], b[1]);
+#pragma unroll
+    for (int c = 2; c < D2; c += 2) {
+        e = fma2(a[c], b[c], e);
+        o = fma2(a[c + 1], b[c + 1], o);
+    }
+    return hsum(add2(e, o));
+}
+// acc += a * s
+__device__ __forceinline__ void axpy_smem(f2 (&acc)[D2], float a, const float *s) {
+    const ulonglong2 *s2 = reinterpret_cast<const ulonglong2 *>(s);
+    const f2 a2 = pk(a, a);
+#pragma unroll
+    for (int c = 0; c < D2 / 2; ++c) {
+        const ulonglong2 t = s2[c];
+        acc[2 * c] = fma2(a2, t.x, acc[2 * c]);
+        acc[2 * c + 1] = fma2(a2, t.y, acc[2 * c + 1]);
+    }
+}
+
+__device__ __forceinline__ void lds_row(f2 (&r)[D2], const float *s) {
+    const ulonglong2 *s2 = reinterpret_cast<const ulonglong2 *>(s);
+#pragma unroll
+    for (int c = 0; c < D2 / 2; ++c) {
+        const ulonglong2 t = s2[c];
+        r[2 * c] = t.x;
+        r[2 * c + 1] = t.y;
+    }
+}
+__device__ __forceinline__ void axpy_reg(f2 (&acc)[D2], float a, const f2 (&x)[D2]) {
+    const f2 a2 = pk(a, a);
+#pragma unroll
+    for (int c = 0; c < D2; ++c) acc[c] = fma2(a2, x[c], acc[c]);
 }
 
 // Stage rows [r0, r0+KT) of head h of a (B,M,H*D) tensor into dst[KT][D] (zero beyond M), scaled by `mul`.
@@ -69,22 +145,28 @@ __device__ __forceinline__ void stage_tile(float *dst, const float *src, int b, 
     }
 }
 
+// R rows (queries, or keys in pass B) per thread: every streamed shared-memory row is loaded ONCE per thread and used
+// for R rows, which halves the LDS.128 traffic per score at R = 2 (the kernels are bound by shared-memory return
+// bandwidth, not by the FMA pipe, once the math is FFMA2).  Row r of a thread is  blockIdx.x*QT*R + r*QT + tid.
+template <int R>
 __global__ void __launch_bounds__(QT) attn_fwd_kernel(const float *__restrict__ q, const float *__restrict__ k,
                                                        const float *__restrict__ v, float *__restrict__ o,
                                                        float *__restrict__ lse, int M, int H, float scale2) {
     __shared__ __align__(16) float ks[KT * D];
     __shared__ __align__(16) float vs[KT * D];
     const int b = blockIdx.z, h = blockIdx.y;
-    const int i = blockIdx.x * QT + threadIdx.x;
-    const int ic = min(i, M - 1);
-    float qr[D], acc[D];
-    load_row(q + (((size_t)b * M + ic) * H + h) * D, qr);
+    int i[R];
+    f2 qr[R][D2], acc[R][D2];
+    float m[R], l[R];
 #pragma unroll
-    for (int c = 0; c < D; ++c) {
-        qr[c] *= scale2;  // scores in the log2 domain: (q.k) / sqrt(d) * log2(e)
-        acc[c] = 0.f;
+    for (int r = 0; r < R; ++r) {
+        i[r] = (blockIdx.x * R + r) * QT + threadIdx.x;
+        load_row(q + (((size_t)b * M + min(i[r], M - 1)) * H + h) * D, qr[r]);
+        scale_row(qr[r], scale2);  // scores in the log2 domain: (q.k) / sqrt(d) * log2(e)
+        zero_row(acc[r]);
+        m[r] = -INFINITY;
+        l[r] = 0.f;
     }
-    float m = -INFINITY, l = 0.f;
     for (int j0 = 0; j0 < M; j0 += KT) {
         __syncthreads();
         stage_tile(ks, k, b, h, H, M, j0, 1.f);
@@ -92,37 +174,52 @@ __global__ void __launch_bounds__(QT) attn_fwd_kernel(const float *__restrict__ 
         __syncthreads();
         const int nk = min(KT, M - j0);
         for (int jb = 0; jb < nk; jb += KB) {
-            float s[KB];
-            float mb = -INFINITY;
+            float s[R][KB];
+            float mn[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) mn[r] = m[r];
 #pragma unroll
             for (int u = 0; u < KB; ++u) {
-                s[u] = jb + u < nk ? dot_smem(qr, ks + (jb + u) * D) : -INFINITY;
-                mb = fmaxf(mb, s[u]);
+                f2 row[D2];
+                lds_row(row, ks + (jb + u) * D);
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    s[r][u] = jb + u < nk ? dot_reg(qr[r], row) : -INFINITY;
+                    mn[r] = fmaxf(mn[r], s[r][u]);
+                }
             }
-            const float mn = fmaxf(m, mb);
-            const float corr = ex2(m - mn);  // first block: m = -inf, mn finite -> 0
-            m = mn;
-            l *= corr;
 #pragma unroll
-            for (int c = 0; c < D; ++c) acc[c] *= corr;
+            for (int r = 0; r < R; ++r) {
+                const float corr = ex2(m[r] - mn[r]);  // first block: m = -inf, mn finite -> 0
+                m[r] = mn[r];
+                l[r] *= corr;
+                scale_row(acc[r], corr);
+            }
 #pragma unroll
             for (int u = 0; u < KB; ++u) {
-                const float p = ex2(s[u] - mn);
-                l += p;
-                axpy_smem(acc, p, vs + (jb + u) * D);
+                f2 row[D2];
+                lds_row(row, vs + (jb + u) * D);
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const float p = ex2(s[r][u] - mn[r]);
+                    l[r] += p;
+                    axpy_reg(acc[r], p, row);
+                }
             }
         }
     }
-    if (i < M) {
-        const float inv = 1.f / l;
 #pragma unroll
-        for (int c = 0; c < D; ++c) acc[c] *= inv;
-        store_row(o + (((size_t)b * M + i) * H + h) * D, acc);
-        lse[((size_t)b * H + h) * M + i] = m + log2f(l);
+    for (int r = 0; r < R; ++r) {
+        if (i[r] < M) {
+            scale_row(acc[r], 1.f / l[r]);
+            store_row(o + (((size_t)b * M + i[r]) * H + h) * D, acc[r]);
+            lse[((size_t)b * H + h) * M + i[r]] = m[r] + log2f(l[r]);
+        }
     }
 }
 
 // pass A: dq_i = scale * sum_j p_ij (dO_i.v_j - delta_i) k_j ; delta_i = dO_i . O_i
+template <int R>
 __global__ void __launch_bounds__(QT) attn_bwd_dq_kernel(const float *__restrict__ q, const float *__restrict__ k,
                                                           const float *__restrict__ v, const float *__restrict__ o,
                                                           const float *__restrict__ dout, const float *__restrict__ lse,
@@ -131,25 +228,26 @@ __global__ void __launch_bounds__(QT) attn_bwd_dq_kernel(const float *__restrict
     __shared__ __align__(16) float ks[KT * D];
     __shared__ __align__(16) float vs[KT * D];
     const int b = blockIdx.z, h = blockIdx.y;
-    const int i = blockIdx.x * QT + threadIdx.x;
-    const int ic = min(i, M - 1);
-    const size_t row = (((size_t)b * M + ic) * H + h) * D;
-    float qr[D], dor[D], acc[D];
-    load_row(q + row, qr);
-    load_row(dout + row, dor);
-    float dl = 0.f;
-    {
-        float orow[D];
-        load_row(o + row, orow);
+    int i[R];
+    size_t row[R];
+    f2 qr[R][D2], dor[R][D2], acc[R][D2];
+    float dl[R], L[R];
 #pragma unroll
-        for (int c = 0; c < D; ++c) dl = fmaf(dor[c], orow[c], dl);
+    for (int r = 0; r < R; ++r) {
+        i[r] = (blockIdx.x * R + r) * QT + threadIdx.x;
+        const int ic = min(i[r], M - 1);
+        row[r] = (((size_t)b * M + ic) * H + h) * D;
+        load_row(q + row[r], qr[r]);
+        load_row(dout + row[r], dor[r]);
+        {
+            f2 orow[D2];
+            load_row(o + row[r], orow);
+            dl[r] = dot_reg(dor[r], orow);
+        }
+        scale_row(qr[r], scale2);
+        zero_row(acc[r]);
+        L[r] = lse[((size_t)b * H + h) * M + ic];
     }
-#pragma unroll
-    for (int c = 0; c < D; ++c) {
-        qr[c] *= scale2;
-        acc[c] = 0.f;
-    }
-    const float L = lse[((size_t)b * H + h) * M + ic];
     for (int j0 = 0; j0 < M; j0 += KT) {
         __syncthreads();
         stage_tile(ks, k, b, h, H, M, j0, 1.f);
@@ -158,20 +256,29 @@ __global__ void __launch_bounds__(QT) attn_bwd_dq_kernel(const float *__restrict
         const int nk = min(KT, M - j0);
 #pragma unroll 4
         for (int j = 0; j < nk; ++j) {
-            const float p = ex2(dot_smem(qr, ks + j * D) - L);
-            const float dp = dot_smem(dor, vs + j * D);
-            axpy_smem(acc, p * (dp - dl), ks + j * D);
+            f2 kr[D2], vr[D2];
+            lds_row(kr, ks + j * D);
+            lds_row(vr, vs + j * D);
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const float p = ex2(dot_reg(qr[r], kr) - L[r]);
+                const float dp = dot_reg(dor[r], vr);
+                axpy_reg(acc[r], p * (dp - dl[r]), kr);
+            }
         }
     }
-    if (i < M) {
 #pragma unroll
-        for (int c = 0; c < D; ++c) acc[c] *= scale;
-        store_row(dq + row, acc);
-        delta[((size_t)b * H + h) * M + i] = dl;
+    for (int r = 0; r < R; ++r) {
+        if (i[r] < M) {
+            scale_row(acc[r], scale);
+            store_row(dq + row[r], acc[r]);
+            delta[((size_t)b * H + h) * M + i[r]] = dl[r];
+        }
     }
 }
 
 // pass B: dv_j = sum_i p_ij dO_i ; dk_j = scale * sum_i p_ij (dO_i.v_j - delta_i) q_i
+template <int R>
 __global__ void __launch_bounds__(QT) attn_bwd_dkv_kernel(const float *__restrict__ q, const float *__restrict__ k,
                                                            const float *__restrict__ v, const float *__restrict__ dout,
                                                            const float *__restrict__ lse, const float *__restrict__ delta,
@@ -181,14 +288,18 @@ __global__ void __launch_bounds__(QT) attn_bwd_dkv_kernel(const float *__restric
     __shared__ __align__(16) float dos[KT * D];
     __shared__ __align__(8) float2 ld[KT];        // (lse, delta)
     const int b = blockIdx.z, h = blockIdx.y;
-    const int j = blockIdx.x * QT + threadIdx.x;
-    const int jc = min(j, M - 1);
-    const size_t row = (((size_t)b * M + jc) * H + h) * D;
-    float kr[D], vr[D], dkr[D], dvr[D];
-    load_row(k + row, kr);
-    load_row(v + row, vr);
+    int j[R];
+    size_t row[R];
+    f2 kr[R][D2], vr[R][D2], dkr[R][D2], dvr[R][D2];
 #pragma unroll
-    for (int c = 0; c < D; ++c) dkr[c] = dvr[c] = 0.f;
+    for (int r = 0; r < R; ++r) {
+        j[r] = (blockIdx.x * R + r) * QT + threadIdx.x;
+        row[r] = (((size_t)b * M + min(j[r], M - 1)) * H + h) * D;
+        load_row(k + row[r], kr[r]);
+        load_row(v + row[r], vr[r]);
+        zero_row(dkr[r]);
+        zero_row(dvr[r]);
+    }
     for (int i0 = 0; i0 < M; i0 += KT) {
         __syncthreads();
         stage_tile(qs, q, b, h, H, M, i0, scale2);
@@ -200,21 +311,29 @@ __global__ void __launch_bounds__(QT) attn_bwd_dkv_kernel(const float *__restric
         }
         __syncthreads();
         const int nq = min(KT, M - i0);
-#pragma unroll 4
+#pragma unroll 2
         for (int i = 0; i < nq; ++i) {
             const float2 Ld = ld[i];
-            const float p = ex2(dot_smem(kr, qs + i * D) - Ld.x);
-            const float dp = dot_smem(vr, dos + i * D);
-            axpy_smem(dvr, p, dos + i * D);
-            axpy_smem(dkr, p * (dp - Ld.y), qs + i * D);
+            f2 qrow[D2], dorow[D2];
+            lds_row(qrow, qs + i * D);
+            lds_row(dorow, dos + i * D);
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const float p = ex2(dot_reg(kr[r], qrow) - Ld.x);
+                const float dp = dot_reg(vr[r], dorow);
+                axpy_reg(dvr[r], p, dorow);
+                axpy_reg(dkr[r], p * (dp - Ld.y), qrow);
+            }
         }
     }
-    if (j < M) {
-        const float ln2 = 0.6931471805599453f;  // qs carries scale*log2(e): dk = scale * sum ds q = ln2 * sum ds qs
+    const float ln2 = 0.6931471805599453f;  // qs carries scale*log2(e): dk = scale * sum ds q = ln2 * sum ds qs
 #pragma unroll
-        for (int c = 0; c < D; ++c) dkr[c] *= ln2;
-        store_row(dk + row, dkr);
-        store_row(dv + row, dvr);
+    for (int r = 0; r < R; ++r) {
+        if (j[r] < M) {
+            scale_row(dkr[r], ln2);
+            store_row(dk + row[r], dkr[r]);
+            store_row(dv + row[r], dvr[r]);
+        }
     }
 }
 
@@ -230,8 +349,13 @@ extern "C" int apb_attn_fwd_f32(const float *q, const float *k, const float *v, 
     if (head_dim != D || B > 65535 || H > 65535) return APB_E_UNSUPPORTED;
     if (!aligned16(q) || !aligned16(k) || !aligned16(v) || !aligned16(o)) return APB_E_INVALID;
     const float scale2 = 1.4426950408889634f / sqrtf((float)D);
-    dim3 grid(apb_div_up(M, QT), H, B);
-    attn_fwd_kernel<<<grid, QT, 0, (cudaStream_t)stream>>>(q, k, v, o, lse, M, H, scale2);
+    if (M > QT) {  // two queries per thread
+        dim3 grid(apb_div_up(M, 2 * QT), H, B);
+        attn_fwd_kernel<2><<<grid, QT, 0, (cudaStream_t)stream>>>(q, k, v, o, lse, M, H, scale2);
+    } else {
+        dim3 grid(apb_div_up(M, QT), H, B);
+        attn_fwd_kernel<1><<<grid, QT, 0, (cudaStream_t)stream>>>(q, k, v, o, lse, M, H, scale2);
+    }
     APB_CHECK_LAUNCH();
     return APB_OK;
 }
@@ -248,11 +372,19 @@ extern "C" int apb_attn_bwd_f32(const float *q, const float *k, const float *v, 
         return APB_E_INVALID;
     const float scale = 1.f / sqrtf((float)D);
     const float scale2 = 1.4426950408889634f * scale;
-    dim3 grid(apb_div_up(M, QT), H, B);
     cudaStream_t st = (cudaStream_t)stream;
-    attn_bwd_dq_kernel<<<grid, QT, 0, st>>>(q, k, v, o, dout, lse, dq, delta, M, H, scale, scale2);
-    APB_CHECK_LAUNCH();
-    attn_bwd_dkv_kernel<<<grid, QT, 0, st>>>(q, k, v, dout, lse, delta, dk, dv, M, H, scale2);
-    APB_CHECK_LAUNCH();
+    if (M > QT) {  // two rows per thread
+        dim3 grid(apb_div_up(M, 2 * QT), H, B);
+        attn_bwd_dq_kernel<2><<<grid, QT, 0, st>>>(q, k, v, o, dout, lse, dq, delta, M, H, scale, scale2);
+        APB_CHECK_LAUNCH();
+        attn_bwd_dkv_kernel<2><<<grid, QT, 0, st>>>(q, k, v, dout, lse, delta, dk, dv, M, H, scale2);
+        APB_CHECK_LAUNCH();
+    } else {
+        dim3 grid(apb_div_up(M, QT), H, B);
+        attn_bwd_dq_kernel<1><<<grid, QT, 0, st>>>(q, k, v, o, dout, lse, dq, delta, M, H, scale, scale2);
+        APB_CHECK_LAUNCH();
+        attn_bwd_dkv_kernel<1><<<grid, QT, 0, st>>>(q, k, v, dout, lse, delta, dk, dv, M, H, scale2);
+        APB_CHECK_LAUNCH();
+    }
     return APB_OK;
 }
