@@ -269,14 +269,21 @@ __global__ void __launch_bounds__(NT) group_grad_rows_kernel(const float *__rest
 #pragma unroll
             for (int ch = 0; ch < CH; ++ch)
                 if (ch < nch) v[ch] = apb_ld_nc_f4(g + (size_t)ch * P + p);
+            // runs of one index inside the thread's four slots are summed in registers first: ball-query rows are
+            // padded with their first index (ball_query_gpu.cu:41-47), and same-address shared atomics serialise
+            const bool e1 = i4.y == i4.x, e2 = i4.z == i4.y, e3 = i4.w == i4.z;
 #pragma unroll
             for (int ch = 0; ch < CH; ++ch) {
                 if (ch < nch) {
                     float *r = rows + (size_t)ch * cnt;
-                    if (a0 < ucnt) atomicAdd(r + a0, v[ch].x);
-                    if (a1 < ucnt) atomicAdd(r + a1, v[ch].y);
-                    if (a2 < ucnt) atomicAdd(r + a2, v[ch].z);
-                    if (a3 < ucnt) atomicAdd(r + a3, v[ch].w);
+                    float x0 = v[ch].x, x1 = v[ch].y, x2 = v[ch].z, x3 = v[ch].w;
+                    if (e3) x2 += x3;
+                    if (e2) x1 += x2;
+                    if (e1) x0 += x1;
+                    if (a0 < ucnt) atomicAdd(r + a0, x0);
+                    if (!e1 && a1 < ucnt) atomicAdd(r + a1, x1);
+                    if (!e2 && a2 < ucnt) atomicAdd(r + a2, x2);
+                    if (!e3 && a3 < ucnt) atomicAdd(r + a3, x3);
                 }
             }
         }

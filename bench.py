@@ -388,6 +388,11 @@ def run_ours(args):
             out["cpu_baseline"] = {"value": round(v, 3), "unit": UNIT, "cores": cores, "kind": "port",
                                    "sample": f"{sample_B} of the {B_PER_GPU} clouds (N={N_POINTS}), 1 warm-up + 1 timed "
                                              f"step, {per:.1f} s/step, torch CPU threads={cores}"}
+        if args.dump_kernels:
+            with open(args.dump_kernels, "w") as f:
+                json.dump([{"call": k[0], "dims": list(k[1]), "launches": v[0], "ms_total": round(v[1], 4),
+                            "us_per_launch": round(v[1] * 1e3 / max(v[0], 1), 2),
+                            "alg_bytes_per_launch": alg_bytes(k[0], k[1])} for k, v in table], f, indent=1)
         print(json.dumps(out), flush=True)
     # Teardown: a captured graph that holds NCCL collectives keeps the communicator busy, and
     # destroy_process_group()/interpreter exit then waits on it forever (seen at N=2 on the box: JSON printed, process
@@ -407,6 +412,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--dump-kernels", default="", help="write the full per-(C-ABI call, dims) timing table of the traced steps here")
     ap.add_argument("--conv", default="tc", choices=["tc", "torch"], help="1x1-conv backend (tcgen05 kernels / cuDNN fp32)")
     ap.add_argument("--no-graph", dest="graph", action="store_false", help="eager launches instead of one CUDA graph")
     ap.add_argument("--no-fused-eval", dest="fused_eval", action="store_false",
