@@ -222,7 +222,9 @@ __global__ void __launch_bounds__(NT) kmax_stats_kernel(const float *__restrict_
         int ax = 0, an = 0;
         if ((K & 3) == 0 && (reinterpret_cast<uintptr_t>(row) & 15) == 0) {
             for (int k = 0; k < K; k += 4) {
-                const float4 v = apb_ld_nc_f4(row + k);
+                // lanes walk 32 different rows (stride K floats): keep the lines in L1 so the second half of every
+                // 32-byte sector is not fetched again (the no-allocate streaming load would re-read it from L2)
+                const float4 v = __ldg(reinterpret_cast<const float4 *>(row + k));
                 const float e[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
@@ -260,25 +262,31 @@ __global__ void __launch_bounds__(NT) bnmax_bwd_kernel(const float *__restrict__
                                                        const float *__restrict__ bcoef, float *__restrict__ dy, int C,
                                                        int M, int K) {
     const int c = blockIdx.y, b = blockIdx.z;
-    const int m = blockIdx.x * NT + threadIdx.x;
-    if (m >= M) return;
-    const size_t rowi = ((size_t)b * C + c) * M + m;
-    const float *row = y + rowi * K;
-    float *out = dy + rowi * K;
-    const float g = gsel[rowi], a0 = a ? a[c] : 0.f, b0 = bcoef ? bcoef[c] : 0.f;
-    const int sel = arg[rowi];
-    if ((K & 3) == 0 && ((reinterpret_cast<uintptr_t>(row) | reinterpret_cast<uintptr_t>(out)) & 15) == 0) {
-        for (int k = 0; k < K; k += 4) {
+    const size_t row0 = ((size_t)b * C + c) * M;
+    const float *src = y ? y + row0 * K : nullptr;
+    float *out = dy + row0 * K;
+    const float a0 = a ? a[c] : 0.f, b0 = bcoef ? bcoef[c] : 0.f;
+    const long long total = (long long)M * K;
+    if ((K & 3) == 0 && ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(out)) & 15) == 0) {
+        // consecutive lanes own consecutive float4s of the (M,K) slab: fully coalesced reads and writes; the K/4 lanes of
+        // one row read the same gsel / arg word (broadcast)
+        for (long long e = ((long long)blockIdx.x * NT + threadIdx.x) * 4; e < total; e += (long long)gridDim.x * NT * 4) {
+            const int m = (int)(e / K), k = (int)(e - (long long)m * K);
+            const float g = __ldg(gsel + row0 + m);
+            const int sel = __ldg(arg + row0 + m) - k;       // slot of the selected element relative to this float4
             float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (bcoef) v = apb_ld_nc_f4(row + k);
-            v.x = fmaf(b0, v.x, a0) + (sel == k + 0 ? g : 0.f);
-            v.y = fmaf(b0, v.y, a0) + (sel == k + 1 ? g : 0.f);
-            v.z = fmaf(b0, v.z, a0) + (sel == k + 2 ? g : 0.f);
-            v.w = fmaf(b0, v.w, a0) + (sel == k + 3 ? g : 0.f);
-            *reinterpret_cast<float4 *>(out + k) = v;
+            if (bcoef) v = apb_ld_nc_f4(src + e);
+            v.x = fmaf(b0, v.x, a0) + (sel == 0 ? g : 0.f);
+            v.y = fmaf(b0, v.y, a0) + (sel == 1 ? g : 0.f);
+            v.z = fmaf(b0, v.z, a0) + (sel == 2 ? g : 0.f);
+            v.w = fmaf(b0, v.w, a0) + (sel == 3 ? g : 0.f);
+            *reinterpret_cast<float4 *>(out + e) = v;
         }
     } else {
-        for (int k = 0; k < K; ++k) out[k] = fmaf(b0, bcoef ? __ldg(row + k) : 0.f, a0) + (sel == k ? g : 0.f);
+        for (long long e = (long long)blockIdx.x * NT + threadIdx.x; e < total; e += (long long)gridDim.x * NT) {
+            const int m = (int)(e / K), k = (int)(e - (long long)m * K);
+            out[e] = fmaf(b0, bcoef ? __ldg(src + e) : 0.f, a0) + (__ldg(arg + row0 + m) == k ? __ldg(gsel + row0 + m) : 0.f);
+        }
     }
 }
 
@@ -432,7 +440,7 @@ extern "C" int apb_bnmax_bwd_f32(const float *y, const float *gsel, const int32_
     if (B == 0 || C == 0 || M == 0) return APB_OK;
     if (!gsel || !arg || !dy || (bcoef && !y)) return APB_E_INVALID;
     if (!grid_ok(B, C)) return APB_E_UNSUPPORTED;
-    dim3 grid(apb_div_up(M, NT), C, B);
+    dim3 grid(min(apb_div_up((long long)M * K, NT * 4), 64), C, B);
     bnmax_bwd_kernel<<<grid, NT, 0, (cudaStream_t)stream>>>(y, gsel, arg, a, bcoef, dy, C, M, K);
     APB_CHECK_LAUNCH();
     return APB_OK;
