@@ -206,6 +206,98 @@ __global__ void __launch_bounds__(NT) bn_bwd_apply_kernel(const float *__restric
     }
 }
 
+// ---- short rows (P <= kSmallP, e.g. the imitator's anchor head: (32, 1024, 4)) -----------------------------------------
+// The kernels above give every (b, c) row its own CTA; with a handful of elements per row that is tens of thousands
+// of one-thread CTAs (35-50 us for 512 KB).  Here a THREAD owns a (b, c) row: thread <-> channel, blockIdx.y = b, so a
+// warp reads 32*P contiguous floats.  Same math; per-channel sums still meet in the fp64 atomics.
+constexpr int kSmallP = 64;
+
+__global__ void __launch_bounds__(NT) bn_stats_small_kernel(const float *__restrict__ x, double *__restrict__ stats,
+                                                            int C, int P) {
+    const int c = blockIdx.x * NT + threadIdx.x, b = blockIdx.y;
+    if (c >= C) return;
+    const float *row = x + ((size_t)b * C + c) * P;
+    float s = 0.f, q = 0.f;
+    for (int i = 0; i < P; ++i) {
+        const float v = __ldg(row + i);
+        s += v;
+        q += v * v;
+    }
+    atomicAdd(stats + 2 * c, (double)s);
+    atomicAdd(stats + 2 * c + 1, (double)q);
+}
+
+__global__ void __launch_bounds__(NT) bn_apply_small_kernel(const BnApplyParams p) {
+    const int c = blockIdx.x * NT + threadIdx.x, b = blockIdx.y;
+    if (c >= p.C) return;
+    const double mean_d = p.stats[2 * c] * p.inv_count;
+    double var_d = p.stats[2 * c + 1] * p.inv_count - mean_d * mean_d;
+    if (var_d < 0.0) var_d = 0.0;
+    const float mean = (float)mean_d;
+    const float rstd = (float)(1.0 / sqrt(var_d + (double)p.eps));
+    const float scale = p.gamma[c] * rstd;
+    const float shift = p.beta[c] - mean * scale;
+    if (b == 0) {
+        p.save_mean[c] = mean;
+        p.save_rstd[c] = rstd;
+        if (p.running_mean) {
+            p.running_mean[c] = (1.f - p.momentum) * p.running_mean[c] + p.momentum * mean;
+            p.running_var[c] = (1.f - p.momentum) * p.running_var[c] + p.momentum * (float)(var_d * p.unbias);
+        }
+    }
+    const int P = (int)p.P;
+    const float *row = p.x + ((size_t)b * p.C + c) * P;
+    float *out = p.y + ((size_t)b * p.C + c) * P;
+    for (int i = 0; i < P; ++i) {
+        const float v = fmaf(__ldg(row + i), scale, shift);
+        out[i] = p.relu ? fmaxf(v, 0.f) : v;
+    }
+}
+
+__global__ void __launch_bounds__(NT) bn_bwd_reduce_small_kernel(const float *__restrict__ x,
+                                                                 const float *__restrict__ dy,
+                                                                 const float *__restrict__ y,
+                                                                 const float *__restrict__ save_mean,
+                                                                 const float *__restrict__ save_rstd,
+                                                                 double *__restrict__ stats2, int C, int P) {
+    const int c = blockIdx.x * NT + threadIdx.x, b = blockIdx.y;
+    if (c >= C) return;
+    const size_t off = ((size_t)b * C + c) * P;
+    const float mean = save_mean[c], rstd = save_rstd[c];
+    float s = 0.f, q = 0.f;
+    for (int i = 0; i < P; ++i) {
+        float g = __ldg(dy + off + i);
+        if (y && !(__ldg(y + off + i) > 0.f)) g = 0.f;
+        s += g;
+        q += g * (__ldg(x + off + i) - mean);
+    }
+    q *= rstd;
+    atomicAdd(stats2 + 2 * c, (double)s);
+    atomicAdd(stats2 + 2 * c + 1, (double)q);
+}
+
+__global__ void __launch_bounds__(NT) bn_bwd_apply_small_kernel(const float *__restrict__ x,
+                                                                const float *__restrict__ dy,
+                                                                const float *__restrict__ y,
+                                                                const float *__restrict__ save_mean,
+                                                                const float *__restrict__ save_rstd,
+                                                                const float *__restrict__ gamma,
+                                                                const double *__restrict__ stats2, double inv_count,
+                                                                float *__restrict__ dx, int C, int P) {
+    const int c = blockIdx.x * NT + threadIdx.x, b = blockIdx.y;
+    if (c >= C) return;
+    const size_t off = ((size_t)b * C + c) * P;
+    const float mean = save_mean[c], rstd = save_rstd[c];
+    const float k0 = gamma[c] * rstd;
+    const float m1 = (float)(stats2[2 * c] * inv_count);
+    const float m2 = (float)(stats2[2 * c + 1] * inv_count) * rstd;
+    for (int i = 0; i < P; ++i) {
+        float g = __ldg(dy + off + i);
+        if (y && !(__ldg(y + off + i) > 0.f)) g = 0.f;
+        dx[off + i] = k0 * (g - m1 - (__ldg(x + off + i) - mean) * m2);
+    }
+}
+
 // ---- BatchNorm -> max over K: statistics + per-(b,c,m) extrema in one read pass ------------------------------------
 // y (B, C, M, K): thread <-> one (b,c,m) row of K contiguous values.
 // vmax/vmin (B,C,M) f32; arg (B,C,M) int32 = argmax | (argmin << 16), first index on ties; stats[c] += (sum, sumsq).
@@ -372,6 +464,11 @@ extern "C" int apb_bn_stats_f32(const float *x, double *stats, int B, int C, lon
     if (B == 0 || C == 0 || P == 0) return APB_OK;
     if (!x || !stats) return APB_E_INVALID;
     if (!grid_ok(B, C)) return APB_E_UNSUPPORTED;
+    if (P <= kSmallP) {
+        bn_stats_small_kernel<<<dim3(apb_div_up(C, NT), B), NT, 0, (cudaStream_t)stream>>>(x, stats, C, (int)P);
+        APB_CHECK_LAUNCH();
+        return APB_OK;
+    }
     dim3 grid(apb_div_up(P, CHUNK), C, B);
     bn_stats_kernel<<<grid, NT, 0, (cudaStream_t)stream>>>(x, stats, C, P);
     APB_CHECK_LAUNCH();
@@ -389,6 +486,11 @@ extern "C" int apb_bn_apply_f32(const float *x, const double *stats, const float
     if (!grid_ok(B, C)) return APB_E_UNSUPPORTED;
     BnApplyParams p{x, y, stats, gamma, beta, eps, 1.0 / count, count > 1.0 ? count / (count - 1.0) : 1.0, relu,
                     save_mean, save_rstd, running_mean, running_var, momentum, C, P};
+    if (P <= kSmallP) {
+        bn_apply_small_kernel<<<dim3(apb_div_up(C, NT), B), NT, 0, (cudaStream_t)stream>>>(p);
+        APB_CHECK_LAUNCH();
+        return APB_OK;
+    }
     dim3 grid(apb_div_up(P, CHUNK), C, B);
     bn_apply_kernel<<<grid, NT, 0, (cudaStream_t)stream>>>(p);
     APB_CHECK_LAUNCH();
@@ -402,6 +504,12 @@ extern "C" int apb_bn_bwd_reduce_f32(const float *x, const float *dy, const floa
     if (B == 0 || C == 0 || P == 0) return APB_OK;
     if (!x || !dy || !save_mean || !save_rstd || !stats2) return APB_E_INVALID;
     if (!grid_ok(B, C)) return APB_E_UNSUPPORTED;
+    if (P <= kSmallP) {
+        bn_bwd_reduce_small_kernel<<<dim3(apb_div_up(C, NT), B), NT, 0, (cudaStream_t)stream>>>(
+            x, dy, y_relu, save_mean, save_rstd, stats2, C, (int)P);
+        APB_CHECK_LAUNCH();
+        return APB_OK;
+    }
     dim3 grid(apb_div_up(P, CHUNK), C, B);
     bn_bwd_reduce_kernel<<<grid, NT, 0, (cudaStream_t)stream>>>(x, dy, y_relu, save_mean, save_rstd, stats2, C, P);
     APB_CHECK_LAUNCH();
@@ -415,6 +523,12 @@ extern "C" int apb_bn_bwd_apply_f32(const float *x, const float *dy, const float
     if (B == 0 || C == 0 || P == 0) return APB_OK;
     if (!x || !dy || !save_mean || !save_rstd || !gamma || !stats2 || !dx) return APB_E_INVALID;
     if (!grid_ok(B, C)) return APB_E_UNSUPPORTED;
+    if (P <= kSmallP) {
+        bn_bwd_apply_small_kernel<<<dim3(apb_div_up(C, NT), B), NT, 0, (cudaStream_t)stream>>>(
+            x, dy, y_relu, save_mean, save_rstd, gamma, stats2, 1.0 / count, dx, C, (int)P);
+        APB_CHECK_LAUNCH();
+        return APB_OK;
+    }
     dim3 grid(apb_div_up(P, CHUNK), C, B);
     bn_bwd_apply_kernel<<<grid, NT, 0, (cudaStream_t)stream>>>(x, dy, y_relu, save_mean, save_rstd, gamma, stats2,
                                                                1.0 / count, dx, C, P);

@@ -25,7 +25,8 @@ def _mk_bn(C, dim, gen, dev):
 
 
 @pytest.mark.parametrize("shape,relu", [((4, 32, 512, 32), True), ((3, 67, 100, 32), False), ((2, 16, 1023), True),
-                                        ((8, 512, 64), True), ((5, 9, 7, 3), True), ((2, 64, 20000), False)])
+                                        ((8, 512, 64), True), ((5, 9, 7, 3), True), ((2, 64, 20000), False),
+                                        ((32, 1024, 4), True), ((4, 300, 1), False), ((3, 40, 65), True)])
 def test_bn_act_matches_torch(cuda_dev, shape, relu):
     from adaptpoint_b200 import tcconv
     gen = torch.Generator().manual_seed(sum(shape))
