@@ -416,6 +416,23 @@ __global__ void __launch_bounds__(NT) affine_kernel(const float *__restrict__ x,
     }
 }
 
+// short rows (P <= kSmallP): thread <-> (b, c) row, see bn_stats_small_kernel
+__global__ void __launch_bounds__(NT) affine_small_kernel(const float *__restrict__ x, const float *__restrict__ y_relu,
+                                                          const float *__restrict__ scale,
+                                                          const float *__restrict__ shift, int relu,
+                                                          float *__restrict__ out, int C, int P) {
+    const int c = blockIdx.x * NT + threadIdx.x, b = blockIdx.y;
+    if (c >= C) return;
+    const size_t off = ((size_t)b * C + c) * P;
+    const float sc = scale[c], sh = shift ? shift[c] : 0.f;
+    for (int i = 0; i < P; ++i) {
+        float v = fmaf(__ldg(x + off + i), sc, sh);
+        if (relu) v = fmaxf(v, 0.f);
+        if (y_relu && !(__ldg(y_relu + off + i) > 0.f)) v = 0.f;
+        out[off + i] = v;
+    }
+}
+
 bool grid_ok(int B, int C) { return B <= 65535 && C <= 65535; }
 
 }  // namespace
@@ -566,6 +583,12 @@ extern "C" int apb_affine_f32(const float *x, const float *mask_relu, const floa
     if (B == 0 || C == 0 || P == 0) return APB_OK;
     if (!x || !scale || !out) return APB_E_INVALID;
     if (!grid_ok(B, C)) return APB_E_UNSUPPORTED;
+    if (P <= kSmallP) {
+        affine_small_kernel<<<dim3(apb_div_up(C, NT), B), NT, 0, (cudaStream_t)stream>>>(x, mask_relu, scale, shift, relu,
+                                                                                         out, C, (int)P);
+        APB_CHECK_LAUNCH();
+        return APB_OK;
+    }
     dim3 grid(apb_div_up(P, CHUNK), C, B);
     affine_kernel<<<grid, NT, 0, (cudaStream_t)stream>>>(x, mask_relu, scale, shift, relu, out, C, P);
     APB_CHECK_LAUNCH();

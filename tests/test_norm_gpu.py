@@ -126,7 +126,8 @@ def test_model_grads_tc_norm_vs_torch(cuda_dev):
 
 
 @pytest.mark.parametrize("shape,relu,param_grads", [((4, 32, 512, 32), True, True), ((3, 67, 1001), False, True),
-                                                    ((2, 64, 128, 32), True, False)])
+                                                    ((2, 64, 128, 32), True, False), ((32, 512, 1), True, True),
+                                                    ((4, 40, 7), False, True)])
 def test_bn_eval_autograd(cuda_dev, shape, relu, param_grads):
     """Eval-mode BatchNorm (+ReLU) under autograd (the feedback-loss path), with and without parameter gradients."""
     from adaptpoint_b200 import tcconv
