@@ -1,0 +1,129 @@
+#!/usr/bin/env python
+"""Data-parallel training-step throughput of the wider PointNeXt configurations (BASELINE.json configs[3], configs[4]).
+
+  python benchmarks/bench_models.py [--gpus N] [--steps K] [--warmup W] [--cases b-cls,l-cls,xl-seg]
+  (N>1: python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 ... benchmarks/bench_models.py --gpus N)
+
+One step = forward + loss + backward + flat NCCL gradient all-reduce (train.allreduce_grads) + AdamW update of one
+per-GPU batch held in HBM, launched eagerly (no CUDA graph: this is the plain model path a user of
+`build_model(...)` gets).  Timing: CUDA events around the K timed steps, barrier + synchronize on both sides,
+max over ranks; samples/s is the whole job (weak scaling, per-GPU batch fixed).  One JSON line per case on rank 0.
+Inputs are synthetic (seeded unit-ball clouds, xyz + height), weights random-init.  bench.py stays the driver's
+contract (configs[1]); this file only records configs[3]/[4] beside it.
+"""
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+# name -> (CONFIGS key, per-GPU batch, points, classes); shapes of BASELINE.json configs[3] / configs[4]
+CASES = {
+    "b-cls": ("pointnext-b-cls", 8, 8192, 40),
+    "l-cls": ("pointnext-l-cls", 8, 8192, 40),
+    "xl-seg": ("pointnext-xl-seg", 2, 24000, 13),
+}
+
+
+def make_batch(B, N, classes, seg, seed, dev):
+    from adaptpoint_b200.synth import make_clouds
+    pos = make_clouds(B, N, "ball", seed)
+    h = pos[:, :, 1:2] - pos[:, :, 1:2].amin(dim=1, keepdim=True)
+    x = torch.cat([pos, h], -1).transpose(1, 2).contiguous()
+    g = torch.Generator().manual_seed(seed + 77)
+    y = torch.randint(0, classes, (B, N) if seg else (B,), generator=g)
+    return pos.to(dev), x.to(dev), y.to(dev)
+
+
+def run_case(name, args, rank, world, dev):
+    from adaptpoint_b200 import tcconv
+    from adaptpoint_b200.models import build_model
+    from adaptpoint_b200.train import allreduce_grads
+    key, B, N, classes = CASES[name]
+    seg = key.endswith("seg")
+    torch.manual_seed(0)                       # same initial weights on every rank
+    model = build_model(key).to(dev).train()
+    params = [p for p in model.parameters() if p.requires_grad]
+    opt = torch.optim.AdamW(params, lr=1e-3, weight_decay=1e-4, fused=True)
+    pos, x, y = make_batch(B, N, classes, seg, 100 + rank, dev)
+
+    def step():
+        opt.zero_grad(set_to_none=True)
+        with tcconv.conv_backend(args.conv):   # 'tc': 1x1 convs (fwd, dgrad, wgrad) on libapb200's tcgen05 kernels
+            if seg:
+                loss = torch.nn.functional.cross_entropy(model({"pos": pos, "x": x}), y)
+            else:
+                _, loss = model.get_logits_loss({"pos": pos, "x": x}, y)
+            loss.backward()
+        allreduce_grads(params)
+        opt.step()
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        loss = step()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        loss = step()
+    e1.record()
+    barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_step = ms.item() / args.steps
+    peak_gb = torch.cuda.max_memory_allocated() / 2**30
+    if rank == 0:
+        print(json.dumps({
+            "metric": f"pointnext_{name.replace('-', '_')}_train_samples_per_s", "value": round(B * world / ms_step * 1e3, 2),
+            "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": round(ms_step, 3), "higher_is_better": True, "scaling": "weak",
+            "dtype": "tf32" if args.conv == "tc" else "f32",
+            "data": "synthetic", "loss": round(float(loss.detach()), 4), "hbm_peak_alloc_gib": round(peak_gb, 2),
+            "params_m": round(sum(p.numel() for p in params) / 1e6, 3),
+            "config": {"workload": f"{key} fwd+bwd+allreduce+AdamW, B={B}/GPU, N={N}, {classes} classes, eager, "
+                                   f"1x1 convs: {'libapb200 tcgen05 tf32' if args.conv == 'tc' else 'cuDNN fp32'}",
+                       "parallelism": f"dp{world}"}}), flush=True)
+    del model, opt
+    torch.cuda.empty_cache()
+    torch.cuda.reset_peak_memory_stats()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--cases", default="b-cls,xl-seg")
+    ap.add_argument("--conv", default="tc", choices=["tc", "torch"])
+    args = ap.parse_args()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench_models.py needs a CUDA device (no CPU fallback)")
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    try:
+        for name in args.cases.split(","):
+            run_case(name, args, rank, world, dev)
+    finally:
+        if world > 1:
+            torch.cuda.synchronize()
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
