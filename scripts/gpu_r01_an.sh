@@ -1,7 +1,7 @@
 set -x
 mkdir -p gpurun_out
 N=${1:-1}
-for c in b-cls xl-seg l-cls; do
+for c in ${2:-b-cls xl-seg l-cls}; do
   if [ "$N" = 1 ]; then
     timeout 150 python benchmarks/bench_models.py --gpus 1 --steps 5 --warmup 3 --cases $c >> gpurun_out/models_r01_an_n$N.jsonl 2> gpurun_out/models_r01_an_n${N}_$c.err
   else
