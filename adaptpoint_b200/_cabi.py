@@ -45,6 +45,8 @@ _SIGNATURES = {
     "apb_kmax_stats_f32": [_p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
     "apb_attn_fwd_f32": [_p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
     "apb_attn_bwd_f32": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
+    "apb_attn_small_fwd_f32": [_p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
+    "apb_attn_small_bwd_f32": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
     "apb_rowmax_f32": [_p, _p, _p, _ll, _i, _p],
     "apb_bnmax_bwd_f32": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
     "apb_peer_ws_create": [_p, _p],

@@ -337,6 +337,103 @@ __global__ void __launch_bounds__(QT) attn_bwd_dkv_kernel(const float *__restric
     }
 }
 
+
+// ---- few tokens, any head width: the anchor head of the imitator (generator_component4_15.py:534-585 Producefactor:
+// 4 anchors, dim 1024, 4 heads => head_dim 256).  One CTA per (head, batch); the M x M score matrix (M <= 32) lives in
+// shared memory; P is kept for the backward pass ((B,H,M,M) floats).
+constexpr int SM_MAXM = 32;
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__global__ void __launch_bounds__(256) attn_small_fwd_kernel(const float *__restrict__ q, const float *__restrict__ k,
+                                                              const float *__restrict__ v, float *__restrict__ o,
+                                                              float *__restrict__ pout, int M, int H, int Dh,
+                                                              float scale) {
+    __shared__ float S[SM_MAXM][SM_MAXM + 1];
+    const int h = blockIdx.x, b = blockIdx.y;
+    const int C = H * Dh;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = blockDim.x >> 5;
+    const float *qb = q + (size_t)b * M * C + h * Dh, *kb = k + (size_t)b * M * C + h * Dh;
+    const float *vb = v + (size_t)b * M * C + h * Dh;
+    for (int pr = warp; pr < M * M; pr += nwarp) {
+        const int i = pr / M, j = pr - i * M;
+        float acc = 0.f;
+        for (int d = lane; d < Dh; d += 32) acc = fmaf(qb[(size_t)i * C + d], kb[(size_t)j * C + d], acc);
+        acc = warp_sum(acc);
+        if (lane == 0) S[i][j] = acc * scale;
+    }
+    __syncthreads();
+    for (int i = warp; i < M; i += nwarp) {
+        const float x = lane < M ? S[i][lane] : -INFINITY;
+        float mx = x;
+#pragma unroll
+        for (int of = 16; of > 0; of >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, of));
+        const float e = lane < M ? expf(x - mx) : 0.f;
+        const float den = warp_sum(e);
+        if (lane < M) {
+            const float pv = e / den;
+            S[i][lane] = pv;
+            pout[(((size_t)b * H + h) * M + i) * M + lane] = pv;
+        }
+    }
+    __syncthreads();
+    for (int t = threadIdx.x; t < M * Dh; t += blockDim.x) {
+        const int i = t / Dh, d = t - i * Dh;
+        float acc = 0.f;
+        for (int j = 0; j < M; ++j) acc = fmaf(S[i][j], vb[(size_t)j * C + d], acc);
+        o[(size_t)b * M * C + (size_t)i * C + h * Dh + d] = acc;
+    }
+}
+
+__global__ void __launch_bounds__(256) attn_small_bwd_kernel(const float *__restrict__ q, const float *__restrict__ k,
+                                                              const float *__restrict__ v, const float *__restrict__ pin,
+                                                              const float *__restrict__ dout, float *__restrict__ dq,
+                                                              float *__restrict__ dk, float *__restrict__ dv, int M,
+                                                              int H, int Dh, float scale) {
+    __shared__ float P[SM_MAXM][SM_MAXM + 1];
+    __shared__ float dS[SM_MAXM][SM_MAXM + 1];
+    const int h = blockIdx.x, b = blockIdx.y;
+    const int C = H * Dh;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = blockDim.x >> 5;
+    const size_t base = (size_t)b * M * C + h * Dh;
+    const float *qb = q + base, *kb = k + base, *vb = v + base, *gb = dout + base;
+    for (int t = threadIdx.x; t < M * M; t += blockDim.x)
+        P[t / M][t % M] = pin[(((size_t)b * H + h) * M) * M + t];
+    // dP[i][j] = dO_i . V_j
+    for (int pr = warp; pr < M * M; pr += nwarp) {
+        const int i = pr / M, j = pr - i * M;
+        float acc = 0.f;
+        for (int d = lane; d < Dh; d += 32) acc = fmaf(gb[(size_t)i * C + d], vb[(size_t)j * C + d], acc);
+        acc = warp_sum(acc);
+        if (lane == 0) dS[i][j] = acc;
+    }
+    __syncthreads();
+    // dS = P o (dP - rowsum(P o dP)) * scale
+    for (int i = warp; i < M; i += nwarp) {
+        const float pv = lane < M ? P[i][lane] : 0.f, dp = lane < M ? dS[i][lane] : 0.f;
+        const float delta = warp_sum(pv * dp);
+        if (lane < M) dS[i][lane] = pv * (dp - delta) * scale;
+    }
+    __syncthreads();
+    for (int t = threadIdx.x; t < M * Dh; t += blockDim.x) {
+        const int i = t / Dh, d = t - i * Dh;
+        float aq = 0.f, ak = 0.f, av = 0.f;
+        for (int j = 0; j < M; ++j) {
+            aq = fmaf(dS[i][j], kb[(size_t)j * C + d], aq);   // dQ_i = sum_j dS_ij K_j
+            ak = fmaf(dS[j][i], qb[(size_t)j * C + d], ak);   // dK_i = sum_j dS_ji Q_j
+            av = fmaf(P[j][i], gb[(size_t)j * C + d], av);    // dV_i = sum_j P_ji dO_j
+        }
+        const size_t off = base + (size_t)i * C + d;
+        dq[off] = aq;
+        dk[off] = ak;
+        dv[off] = av;
+    }
+}
+
 bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 }  // namespace
@@ -386,5 +483,30 @@ extern "C" int apb_attn_bwd_f32(const float *q, const float *k, const float *v, 
         attn_bwd_dkv_kernel<1><<<grid, QT, 0, st>>>(q, k, v, dout, lse, delta, dk, dv, M, H, scale2);
         APB_CHECK_LAUNCH();
     }
+    return APB_OK;
+}
+
+extern "C" int apb_attn_small_fwd_f32(const float *q, const float *k, const float *v, float *o, float *p, int B, int M,
+                                      int H, int head_dim, apb_stream_t stream) {
+    if (B < 0 || M < 0 || H < 0 || head_dim <= 0) return APB_E_INVALID;
+    if (B == 0 || M == 0 || H == 0) return APB_OK;
+    if (!q || !k || !v || !o || !p) return APB_E_INVALID;
+    if (M > SM_MAXM || B > 65535) return APB_E_UNSUPPORTED;
+    attn_small_fwd_kernel<<<dim3(H, B), 256, 0, (cudaStream_t)stream>>>(q, k, v, o, p, M, H, head_dim,
+                                                                        1.f / sqrtf((float)head_dim));
+    APB_CHECK_LAUNCH();
+    return APB_OK;
+}
+
+extern "C" int apb_attn_small_bwd_f32(const float *q, const float *k, const float *v, const float *p, const float *dout,
+                                      float *dq, float *dk, float *dv, int B, int M, int H, int head_dim,
+                                      apb_stream_t stream) {
+    if (B < 0 || M < 0 || H < 0 || head_dim <= 0) return APB_E_INVALID;
+    if (B == 0 || M == 0 || H == 0) return APB_OK;
+    if (!q || !k || !v || !p || !dout || !dq || !dk || !dv) return APB_E_INVALID;
+    if (M > SM_MAXM || B > 65535) return APB_E_UNSUPPORTED;
+    attn_small_bwd_kernel<<<dim3(H, B), 256, 0, (cudaStream_t)stream>>>(q, k, v, p, dout, dq, dk, dv, M, H, head_dim,
+                                                                        1.f / sqrtf((float)head_dim));
+    APB_CHECK_LAUNCH();
     return APB_OK;
 }

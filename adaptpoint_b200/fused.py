@@ -56,8 +56,18 @@ def pack_bf16(W):
     return out.contiguous(), kp
 
 
+_GENERATION = 0   # bumped by invalidate_packed(): state changes no tensor version records (CUDA-graph replays)
+
+
+def invalidate_packed():
+    """Drop every cached fold: call after parameters / BatchNorm buffers changed behind autograd's version counters
+    (AdaptPointTrainer.step does, for graph replays)."""
+    global _GENERATION
+    _GENERATION += 1
+
+
 def _state_key(mods):
-    key = []
+    key = [_GENERATION]
     for m in mods:
         for t in list(m.parameters()) + list(m.buffers()):
             key.append((t.data_ptr(), t._version))

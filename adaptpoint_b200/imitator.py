@@ -203,8 +203,8 @@ class PointsetGrouper(nn.Module):
 
 class Anchor_selfattention(nn.Module):
     """Multi-head self-attention with an xyz positional embedding (generator_component4_15.py:434-480).
-    softmax(q k^T / sqrt(d)) v runs through torch's fused SDPA, so the (B,heads,M,M) matrix of the mask branch
-    (M = N = 2048) is never materialised."""
+    softmax(q k^T / sqrt(d)) v runs on csrc/attention.cu (ops.self_attention), so the (B,heads,M,M) matrix of the mask
+    branch (M = N = 2048) is never materialised."""
 
     def __init__(self, dim, head_num):
         super().__init__()
@@ -220,9 +220,9 @@ class Anchor_selfattention(nn.Module):
         rel = xyz - xyz.mean(dim=1, keepdim=True)
         emb = self.pos_embedding(rel.permute(0, 2, 1)).permute(0, 2, 1)
         q, k, v = self.to_qkv(x).chunk(3, dim=-1)
-        if x.is_cuda and self.head_dim == 16:      # our flash-style fp32 kernel, token-major in and out
+        if x.is_cuda:      # our fp32 kernels (flash-style for head_dim 16, few-token otherwise), token-major in / out
             o = ops.self_attention(q + emb, k + emb, v + emb, self.head_num)
-        else:
+        else:              # CPU tensors only: the oracle-patched tests and the CPU baseline of bench.py
             split = lambda t: (t + emb).reshape(B, M, self.head_num, self.head_dim).permute(0, 2, 1, 3)
             o = F.scaled_dot_product_attention(split(q), split(k), split(v))
             o = o.permute(0, 2, 1, 3).reshape(B, M, -1)
@@ -250,13 +250,18 @@ class Producefactor(nn.Module):
         return self.prob_head(feat.permute(0, 2, 1)).permute(0, 2, 1)
 
 
-def gumbel_softmax_hard(logits, tau, gumbels=None):
-    """F.gumbel_softmax(hard=True) with injectable noise (straight-through one-hot)."""
+def gumbel_softmax_hard(logits, tau, gumbels=None, hard=None):
+    """F.gumbel_softmax(hard=True) with injectable noise (straight-through one-hot).  `hard` (same shape, one-hot)
+    replaces the arg-max decision -- parity tests feed the reference run's decisions so that a near-tie logit cannot
+    flip a point between runs; the gradient still flows through the soft-max of this run."""
     if gumbels is None:
         gumbels = -torch.empty_like(logits, memory_format=torch.legacy_contiguous_format).exponential_().log()
     y_soft = ((logits + gumbels) / tau).softmax(-1)
-    index = y_soft.max(-1, keepdim=True)[1]
-    y_hard = torch.zeros_like(logits, memory_format=torch.legacy_contiguous_format).scatter_(-1, index, 1.0)
+    if hard is None:
+        index = y_soft.max(-1, keepdim=True)[1]
+        y_hard = torch.zeros_like(logits, memory_format=torch.legacy_contiguous_format).scatter_(-1, index, 1.0)
+    else:
+        y_hard = hard.to(logits.dtype)
     return y_hard - y_soft.detach() + y_soft
 
 
@@ -290,7 +295,7 @@ class SAComponent(nn.Module):
         self.extract_global_feat_masking = nn.Sequential(TcConv1d(last, 3, 1, bias=False), TcBatchNorm1d(3))
         self.fuse_masking = nn.Sequential(TcConv1d(6, 2, 1, bias=False), TcBatchNorm1d(2))
 
-    def forward(self, x, a_index=None, gumbels=None):
+    def forward(self, x, a_index=None, gumbels=None, hard_mask=None):
         """x (B,N,3), a_index (B,M) -> prob (B,M,9), masking (B,N,2) hard one-hot (straight-through)."""
         _, N, _ = x.shape
         a_points = _index_points(x, a_index)
@@ -312,7 +317,7 @@ class SAComponent(nn.Module):
         m_local = self.extract_local_feat_masking(local.permute(0, 2, 1))                    # (B,3,N)
         m_global = self.extract_global_feat_masking(x_list[-1]).max(dim=2, keepdim=True)[0]    # (B,3,1)
         masking = self.fuse_masking(torch.cat([m_local, m_global.repeat(1, 1, N)], dim=1)).permute(0, 2, 1)
-        return prob, gumbel_softmax_hard(masking, 0.1, gumbels)
+        return prob, gumbel_softmax_hard(masking, 0.1, gumbels, hard_mask)
 
 
 class AdaptPoint_Augmentor(nn.Module):
@@ -333,11 +338,12 @@ class AdaptPoint_Augmentor(nn.Module):
         return dict(dropout=dropout, axis=axis, proj_axis=proj_axis)
 
     def forward(self, xyz, noise=None):
-        """xyz (B,N,3) -> (xyz, xyz_new).  noise: optional dict(dropout, axis, proj_axis[, gumbel])."""
+        """xyz (B,N,3) -> (xyz, xyz_new).  noise: optional dict(dropout, axis, proj_axis[, gumbel][, hard_mask])."""
         B, N, _ = xyz.shape
         dev = xyz.device
         fps_idx, anchor = geometry.sample(xyz, self.num_anchor)
-        probs, masking = self.predict_prob_layer(xyz, fps_idx, None if noise is None else noise.get("gumbel"))
+        probs, masking = self.predict_prob_layer(xyz, fps_idx, None if noise is None else noise.get("gumbel"),
+                                                 None if noise is None else noise.get("hard_mask"))
         noise = self.draw(B) if noise is None else noise
         drop, axis = noise["dropout"].to(dev), noise["axis"].to(dev).float()
         degree = math.pi * (torch.tanh(probs[:, :, 0:3]) * self.w_R_range) / 180.0 * drop[:, :, 0:1]

@@ -190,9 +190,39 @@ class SelfAttention16(Function):
         return dq, dk, dv, None
 
 
+class SelfAttentionSmall(Function):
+    @staticmethod
+    def forward(ctx, q, k, v, heads: int):
+        """Few tokens (M <= 32), any head width (apb_attn_small_fwd_f32): the imitator's anchor head."""
+        q, k, v = (t.detach().contiguous().float() for t in (q, k, v))
+        B, M, C = q.shape
+        o = torch.empty_like(q)
+        p = torch.empty((B, heads, M, M), dtype=torch.float32, device=q.device)
+        _cabi.call("apb_attn_small_fwd_f32", [q, k, v, o, p, B, M, heads, C // heads], q.device)
+        ctx.save_for_backward(q, k, v, p)
+        ctx.heads = heads
+        return o
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        q, k, v, p = ctx.saved_tensors
+        B, M, C = q.shape
+        go = grad_out.detach().contiguous().float()
+        dq, dk, dv = torch.empty_like(q), torch.empty_like(q), torch.empty_like(q)
+        _cabi.call("apb_attn_small_bwd_f32", [q, k, v, p, go, dq, dk, dv, B, M, ctx.heads, C // ctx.heads], q.device)
+        return dq, dk, dv, None
+
+
 def self_attention(q, k, v, heads):
-    """Multi-head self-attention over (B,M,C) token-major tensors, head_dim = C/heads = 16."""
-    return SelfAttention16.apply(q, k, v, heads)
+    """Multi-head self-attention softmax(q k^T / sqrt(d)) v over (B,M,C) token-major tensors: the flash-style kernel for
+    head_dim 16 (any M), the few-token kernel for M <= 32 (any head_dim).  Nothing else occurs on the path, and there
+    is no library fallback."""
+    if q.shape[-1] // heads == 16:
+        return SelfAttention16.apply(q, k, v, heads)
+    if q.shape[1] <= 32:
+        return SelfAttentionSmall.apply(q, k, v, heads)
+    raise _cabi.ApbError(f"self_attention: head_dim {q.shape[-1] // heads} with {q.shape[1]} tokens is outside the "
+                         "kernel family (head_dim 16, or <= 32 tokens)")
 
 
 def torch_grouping_operation(features, idx):

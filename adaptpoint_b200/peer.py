@@ -33,26 +33,59 @@ class PeerAllreduce:
         with torch.cuda.device(self.device):
             status = lib.apb_peer_ws_create(ctypes.byref(mine), handle)
         self._own = mine.value if status == 0 else None
-        handles = [None] * self.world
-        dist.all_gather_object(handles, (self.rank, bytes(handle) if status == 0 else None, os.uname().nodename),
-                               group=self.group)
-        if any(h[1] is None for h in handles):           # the same verdict on every rank
-            raise _cabi.ApbError(f"apb_peer_ws_create failed on a rank (mine: status {status})")
-        if len({h[2] for h in handles}) != 1:
-            raise _cabi.ApbError("PeerAllreduce: ranks span several nodes")
-        self._ptrs = (ctypes.c_void_p * self.world)()
-        for r, hb, _ in handles:
-            if r == self.rank:
-                self._ptrs[r] = self._own
-                continue
-            p = ctypes.c_void_p()
-            buf = (ctypes.c_ubyte * 64).from_buffer_copy(hb)
-            with torch.cuda.device(self.device):
-                status = lib.apb_peer_ws_open(buf, ctypes.byref(p))
-            if status != 0:
-                raise _cabi.ApbError(f"apb_peer_ws_open(rank {r}) failed (status {status})")
-            self._ptrs[r] = p.value
+        self._opened = []                       # peer mappings this process opened (closed by close())
+        self._last = None                       # (stream handle, event, capturing) of the previous all-reduce
+        try:
+            handles = [None] * self.world
+            dist.all_gather_object(handles, (self.rank, bytes(handle) if status == 0 else None, os.uname().nodename),
+                                   group=self.group)
+            if any(h[1] is None for h in handles):           # the same verdict on every rank
+                raise _cabi.ApbError(f"apb_peer_ws_create failed on a rank (mine: status {status})")
+            if len({h[2] for h in handles}) != 1:
+                raise _cabi.ApbError("PeerAllreduce: ranks span several nodes")
+            self._ptrs = (ctypes.c_void_p * self.world)()
+            for r, hb, _ in handles:
+                if r == self.rank:
+                    self._ptrs[r] = self._own
+                    continue
+                p = ctypes.c_void_p()
+                buf = (ctypes.c_ubyte * 64).from_buffer_copy(hb)
+                with torch.cuda.device(self.device):
+                    status = lib.apb_peer_ws_open(buf, ctypes.byref(p))
+                if status != 0:
+                    raise _cabi.ApbError(f"apb_peer_ws_open(rank {r}) failed (status {status})")
+                self._ptrs[r] = p.value
+                self._opened.append(p.value)
+        except Exception:
+            self.close()                        # no leaked cudaMalloc / IPC mappings on the failure path
+            raise
         self.calls = 0                          # enable() lines the ranks up before the first store can land
+
+    def close(self):
+        """Unmap the peers' workspaces and free this rank's own.  Collective in effect: every rank must have stopped
+        issuing all-reduces (call after a device synchronize + barrier)."""
+        lib = _cabi.load()
+        with torch.cuda.device(self.device):
+            for p in self._opened:
+                lib.apb_peer_ws_close(ctypes.c_void_p(p), 0)
+            self._opened = []
+            if self._own is not None:
+                lib.apb_peer_ws_close(ctypes.c_void_p(self._own), 1)
+                self._own = None
+
+    def _serialise(self, cur):
+        """The two-parity protocol of csrc/peer.cu has ONE sequence counter per workspace: two all-reduces of a rank
+        must never be in flight together.  A call issued on a different stream than the previous one is therefore
+        ordered after it with an event (same-stream calls are ordered already)."""
+        capturing = torch.cuda.is_current_stream_capturing()
+        last = self._last
+        if last is not None and last[0] != cur.cuda_stream and last[2] == capturing:
+            cur.wait_event(last[1])
+        return capturing
+
+    def forget_order(self):
+        """After a device-wide synchronize (capture_graph does one) no earlier all-reduce is in flight."""
+        self._last = None
 
     def supports(self, t):
         return (t.is_cuda and t.device == self.device and t.is_contiguous() and t.numel() <= self.max_elems
@@ -61,11 +94,18 @@ class PeerAllreduce:
     def allreduce_(self, t):
         """In-place sum of `t` over the group on the current stream."""
         lib = _cabi.load()
+        if self._own is None:
+            raise _cabi.ApbError("PeerAllreduce used after close()")
         with torch.cuda.device(self.device):
-            stream = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+            cur = torch.cuda.current_stream(self.device)
+            capturing = self._serialise(cur)
+            stream = ctypes.c_void_p(cur.cuda_stream)
             status = lib.apb_peer_allreduce(ctypes.c_void_p(t.data_ptr()), t.numel(),
                                             1 if t.dtype == torch.float64 else 0, self._ptrs, self.world, self.rank,
                                             stream)
+            ev = torch.cuda.Event()
+            ev.record(cur)
+            self._last = (cur.cuda_stream, ev, capturing)
         if status != 0:
             raise _cabi.ApbError(f"apb_peer_allreduce failed: {lib.apb_error_string(status).decode()} ({status})")
         _cabi.LAUNCHES += 1
@@ -101,6 +141,14 @@ def enable(group=None):
             ctx = None
     _CTX[key] = ctx
     return ctx
+
+
+def disable(group=None):
+    """Close and forget the peer context of `group` (every rank, after a synchronize + barrier)."""
+    g = group if group is not None else (dist.group.WORLD if dist.is_initialized() else None)
+    ctx = _CTX.pop(id(g), None)
+    if ctx is not None:
+        ctx.close()
 
 
 def get(group=None):

@@ -7,8 +7,10 @@ backend switch is "tc", run
     y  = W x (+b)            apb_pwconv_fwd_tf32 | _bf16   (tf32 or bf16 operands, fp32 accumulate, tcgen05)
     gx = W^T gy              the same kernel on the transposed weights
     gW = gy x^T              apb_pwconv_wgrad_tf32 (TF32, both operands TMA-fed)
-Numerics: tf32 (default) ~1e-3 relative per layer; bf16 2e-2 (BASELINE.json north_star, "bf16 MLP path").  With the switch at "torch" (default) they
-are plain nn.Conv{1,2}d (strict fp32 parity tests use that).
+Numerics: tf32 (default) ~1e-3 relative per layer; bf16 2e-2 (BASELINE.json north_star, "bf16 MLP path").  "tc" is
+the product path and the default for CUDA tensors; the switch at "torch" turns the layers back into plain
+nn.Conv{1,2}d -- a TEST-ONLY strict-fp32 mode (tests/, the golden parity runs); CPU tensors (the oracle-patched CPU
+tests and the CPU baseline of bench.py) always take the nn.Conv path, there is no CPU product path.
 """
 import contextlib
 
@@ -19,7 +21,7 @@ from torch.autograd import Function
 from . import _cabi
 from .fused import pack_bf16
 
-_BACKEND = "torch"
+_BACKEND = "tc"
 _PRECISION = "tf32"   # operands of y = W x and gx = W^T gy on the "tc" backend: "tf32" (default) or "bf16"
 _MAX_N = 512  # accumulator columns of one kernel call
 
@@ -27,8 +29,8 @@ _MAX_N = 512  # accumulator columns of one kernel call
 def set_conv_precision(name):
     """'tf32' (10-bit mantissa operands: what the reference's cuDNN convs use by default on Ampere+) or 'bf16'
     (BASELINE.json's "bf16 MLP path", 2e-2).  bf16 operand rounding flips enough max-pool / ReLU routing decisions
-    in PointNeXt to turn the weight gradients of the early stages ~40 degrees (cos 0.75 vs fp32, measured in
-    scripts/dbg_tc2.py against an exact torch emulation), tf32 keeps cos > 0.999, at the same HBM-bound speed."""
+    in PointNeXt to turn the weight gradients of the early stages ~40 degrees (cos 0.75 vs fp32, measured against
+    an exact torch emulation in round 1), tf32 keeps cos > 0.999, at the same HBM-bound speed."""
     global _PRECISION
     if name not in ("tf32", "bf16"):
         raise ValueError(name)
@@ -40,7 +42,7 @@ def get_conv_precision():
 
 
 def set_conv_backend(name):
-    """'torch' (cuDNN, fp32) or 'tc' (libapb200 tensor-core kernels)."""
+    """'tc' (libapb200 tensor-core kernels: the product path, default) or 'torch' (cuDNN fp32: test-only strict mode)."""
     global _BACKEND
     if name not in ("torch", "tc"):
         raise ValueError(name)

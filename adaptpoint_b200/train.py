@@ -11,8 +11,9 @@ cfgs/scanobjectnn/default.yaml:35-52.  Deliberate differences (SURVEY.md 2.2, 8f
     iteration and rebuilds a DataLoader per epoch);
   * data parallelism is explicit: per-rank batch fixed, gradients of every updated network are averaged with
     ONE flat NCCL all-reduce per optimizer step (the reference wraps in DDP but calls `model.module....`, so
-    its reducer never fires), BatchNorm becomes SyncBatchNorm when world_size > 1 like the reference
-    (main.py:27);
+    its reducer never fires); the CLASSIFIER's BatchNorm becomes SyncBatchNorm when world_size > 1, as in the
+    reference (main.py:27 / train_autoaug.py:276 convert the classifier only; get_gan_model wraps the imitator and
+    the discriminator in plain DDP, so their BatchNorm statistics stay per rank -- here too);
   * logging / TensorBoard / h5 dumps are left out.
 """
 import copy
@@ -21,13 +22,13 @@ import torch
 import torch.distributed as dist
 import torch.nn as nn
 
-from . import geometry, norm, ops, peer, tcconv
+from . import fused, geometry, norm, ops, peer, tcconv
 from .imitator import AdaptPoint_Augmentor, PointDiscriminator1, PointWOLF_classversion
 from .models import SmoothCrossEntropy, build_model
 
 ADAPTPOINT_CFG = dict(
     model="pointnext-s", num_points=1024, num_classes=15, in_channels=4, batch_size=32, loader_points=2048,
-    lr=0.002, weight_decay=0.05, grad_norm_clip=10.0, label_smoothing=0.3, epochs=300,
+    lr=0.002, min_lr=1e-4, weight_decay=0.05, grad_norm_clip=10.0, label_smoothing=0.3, epochs=300,
     pointwolf=dict(w_num_anchor=4, w_sigma=0.5, w_R_range=10, w_S_range=3, w_T_range=0.25),
     adaptmodel_gan=dict(w_num_anchor=4, w_sigma=0.5, w_R_range=10, w_S_range=3, w_T_range=0.25),
     adaptmodel_dis=dict(num_classes=15, normal_channel=False),
@@ -40,7 +41,7 @@ def _world():
     return dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
 
 
-def allreduce_grads(params, bucket=None):
+def allreduce_grads(params):
     """Average gradients over ranks with one flat all-reduce (NCCL over NVLink on the GPU box, gloo in tests)."""
     world = _world()
     if world == 1:
@@ -64,6 +65,15 @@ def hard_ratio(epoch, cfg):
     return ap["hardratio_s"] + (ap["hardratio"] - ap["hardratio_s"]) * epoch / cfg["epochs"]
 
 
+def cosine_lr(epoch, cfg):
+    """Cosine decay from cfg['lr'] to cfg['min_lr'] over cfg['epochs'] (the reference's `sched: cosine`,
+    warmup_epochs 0, stepped once per epoch)."""
+    import math
+    lo = cfg.get("min_lr", 1e-4)
+    t = min(max(epoch, 0), cfg["epochs"]) / max(cfg["epochs"], 1)
+    return lo + 0.5 * (cfg["lr"] - lo) * (1.0 + math.cos(math.pi * t))
+
+
 def feedback_loss(classifier, criterion, data_real, data_fake, rho, pred_real=None):
     """|1 - exp(L_fake - rho * L_real)| with the classifier in eval mode but inside autograd
     (ganloss_cls.py:31-65).  `pred_real`: logits of the real batch when the caller already has them."""
@@ -85,9 +95,12 @@ class AdaptPointTrainer:
     """Holds classifier / imitator / discriminator + their optimizers; `step(batch)` = one train_gan iteration
     followed by one train_one_epoch iteration on the generated batch."""
 
-    def __init__(self, cfg=None, device="cuda", fused_eval=False, seed=0, conv_backend="tc", overlap=True):
+    def __init__(self, cfg=None, device="cuda", fused_eval=False, seed=0, conv_backend="tc", overlap=True,
+                 host_gumbel=False):
         """conv_backend: 'tc' = every 1x1 convolution (fwd, dgrad, wgrad) on the tcgen05 kernels of libapb200
-        (bf16/TF32 operands, fp32 accumulation); 'torch' = cuDNN fp32 (strict-parity runs)."""
+        (bf16/TF32 operands, fp32 accumulation); 'torch' = cuDNN fp32 (strict-parity runs).  host_gumbel: draw the
+        mask branch's Gumbel noise with the host generator like every other draw (reproducible runs / tests); default
+        is the reference's device-side draw (F.gumbel_softmax, generator_component4_15.py:714)."""
         self.cfg = copy.deepcopy(ADAPTPOINT_CFG if cfg is None else cfg)
         self.device = torch.device(device)
         self.conv_backend = conv_backend if self.device.type == "cuda" else "torch"
@@ -101,26 +114,30 @@ class AdaptPointTrainer:
             elif self.conv_backend == "tc":    # our BatchNorm kernels all-reduce their (C,2) statistics themselves
                 with torch.cuda.device(self.device):
                     peer.enable()              # ... over NVLink peer memory when the ranks share a node (peer.py)
-                norm.enable_sync(self.classifier)
-                norm.enable_sync(self.generator)
+                norm.enable_sync(self.classifier)     # classifier only: the reference leaves G / D on per-rank BN
             else:
                 self.classifier = nn.SyncBatchNorm.convert_sync_batchnorm(self.classifier)
-                self.generator = nn.SyncBatchNorm.convert_sync_batchnorm(self.generator)
             for net in (self.classifier, self.generator, self.discriminator):      # same init on every rank
                 for t in list(net.parameters()) + list(net.buffers()):
                     dist.broadcast(t.data, 0)
         ap = self.cfg["adaptpoint_params"]
         cap = self.device.type == "cuda"      # device-side step counters: required inside a CUDA graph
         kw = {"capturable": True, "fused": True} if cap else {}   # one multi-tensor kernel per optimizer step
-        self.opt_c = torch.optim.AdamW(self.classifier.parameters(), lr=self.cfg["lr"],
+        # learning rates live in device scalars on CUDA: a captured graph reads them at replay time, so `set_lr` /
+        # `set_epoch` (the reference's per-epoch cosine `scheduler.step(epoch)`, train_autoaug.py:431) keep working
+        # after `capture_graph`
+        mk = (lambda v: torch.tensor(float(v), dtype=torch.float32, device=self.device)) if cap else float
+        self._lr = {"c": mk(self.cfg["lr"]), "g": mk(ap["lr_generator"]), "d": mk(ap["lr_discriminator"])}
+        self.opt_c = torch.optim.AdamW(self.classifier.parameters(), lr=self._lr["c"],
                                        weight_decay=self.cfg["weight_decay"], **kw)
-        self.opt_g = torch.optim.Adam(self.generator.parameters(), lr=ap["lr_generator"], betas=(ap["b1"], ap["b2"]),
+        self.opt_g = torch.optim.Adam(self.generator.parameters(), lr=self._lr["g"], betas=(ap["b1"], ap["b2"]),
                                       **kw)
-        self.opt_d = torch.optim.Adam(self.discriminator.parameters(), lr=ap["lr_discriminator"],
+        self.opt_d = torch.optim.Adam(self.discriminator.parameters(), lr=self._lr["d"],
                                       betas=(ap["b1"], ap["b2"]), **kw)
         self.criterion_gan = nn.BCELoss()
         self.criterion = SmoothCrossEntropy(label_smoothing=self.cfg["label_smoothing"])
         self.pointwolf = PointWOLF_classversion(**self.cfg["pointwolf"])
+        self.host_gumbel = host_gumbel
         self.epoch = 0
         self._rho = torch.tensor(float(hard_ratio(0, self.cfg)), device=self.device)   # device scalar: graph-safe
         self._graph = None
@@ -128,6 +145,11 @@ class AdaptPointTrainer:
         self._side = None
         self._geo = None
         self._prepared = None
+        self.grad_probe = None     # tests: callable(name, module) invoked after each backward, before the optimizer step
+
+    def _probe(self, name, module):
+        if self.grad_probe is not None:
+            self.grad_probe(name, module)
 
     def _side_stream(self):
         if self._side is None:
@@ -184,9 +206,29 @@ class AdaptPointTrainer:
         return min({1024: 1200, 4096: 4800, 8192: 8192}[npoints], n_loader_points)
 
     # -- train_autoaug.py:131-207 ---------------------------------------------------------------------------
-    def set_epoch(self, epoch):
+    def set_epoch(self, epoch, schedule_lr=True):
+        """Per-epoch host hook: rho of the feedback loss (ganloss_cls.py:53-54) and, as the reference's
+        `scheduler.step(epoch)` does for the classifier (cosine, cfgs/scanobjectnn/default.yaml:46-50), its lr."""
         self.epoch = epoch
         self._rho.fill_(float(hard_ratio(epoch, self.cfg)))
+        if schedule_lr:
+            self.set_lr(c=cosine_lr(epoch, self.cfg))
+
+    def set_lr(self, c=None, g=None, d=None):
+        """Change the learning rate of the classifier / imitator / discriminator optimizer; graph-safe (the captured
+        optimizer kernels read the device scalars)."""
+        for key, val, opt in (("c", c, self.opt_c), ("g", g, self.opt_g), ("d", d, self.opt_d)):
+            if val is None:
+                continue
+            if isinstance(self._lr[key], torch.Tensor):
+                self._lr[key].fill_(float(val))
+            else:
+                self._lr[key] = float(val)
+                for grp in opt.param_groups:
+                    grp["lr"] = float(val)
+
+    def get_lr(self):
+        return {k: float(v) for k, v in self._lr.items()}
 
     def draw_noise(self, B, n_loader_points):
         """All host-RNG draws of one step, in the order the reference makes them: PointWOLF (pointwolf.py:113-131),
@@ -194,6 +236,8 @@ class AdaptPointTrainer:
         (train_autoaug.py:497, np.random.choice)."""
         npoints = self.cfg["num_points"]
         noise = {"wolf": self.pointwolf.draw(B), "gen": self.generator.draw(B)}
+        if self.host_gumbel:
+            noise["gen"]["gumbel"] = -torch.empty(B, n_loader_points, 2).exponential_().log()
         if n_loader_points > npoints:
             point_all = min({1024: 1200, 4096: 4800, 8192: 8192}[npoints], n_loader_points)
             noise["keep"] = torch.randperm(point_all)[:npoints]
@@ -274,6 +318,7 @@ class AdaptPointTrainer:
         self.opt_g.zero_grad()
         g_loss.backward()
         allreduce_grads(list(G.parameters()))
+        self._probe("generator", G)
         self.opt_g.step()
 
         real_loss = self.criterion_gan(D(inp), real_label)
@@ -282,6 +327,7 @@ class AdaptPointTrainer:
         self.opt_d.zero_grad()
         d_loss.backward()
         allreduce_grads(list(D.parameters()))
+        self._probe("discriminator", D)
         self.opt_d.step()
         C.zero_grad(set_to_none=True)                           # model_pointcloud.zero_grad() (:232)
         return fake_det, g_loss.detach(), d_loss.detach()
@@ -322,6 +368,7 @@ class AdaptPointTrainer:
         logits, loss = model.get_logits_loss(data, target)
         loss.backward()
         allreduce_grads(list(model.parameters()))
+        self._probe("classifier", model)
         if cfg.get("grad_norm_clip"):
             torch.nn.utils.clip_grad_norm_(model.parameters(), cfg["grad_norm_clip"], norm_type=2)
         self.opt_c.step()
@@ -343,6 +390,7 @@ class AdaptPointTrainer:
         After `capture_graph`, the whole step (three forward/backward passes, gradient all-reduces, three optimizer
         updates: ~3000 kernel launches) is ONE CUDA-graph replay; only the host-RNG draws stay on the host."""
         noise = self.draw_noise(points.shape[0], points.shape[1])
+        fused.invalidate_packed()    # parameters / BN statistics change below (a graph replay bumps no tensor version)
         if self._graph is None:
             return self._step_impl(points, label, noise)
         self._g_points.copy_(points, non_blocking=True)
@@ -367,12 +415,25 @@ class AdaptPointTrainer:
                 self._step_impl(self._g_points, self._g_label, self._g_noise)
         torch.cuda.current_stream(self.device).wait_stream(side)
         torch.cuda.synchronize(self.device)
+        ctx = peer.get()
+        if ctx is not None:
+            ctx.forget_order()       # nothing is in flight: the captured all-reduces need no edge to eager ones
         graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(graph):
             out = self._step_impl(self._g_points, self._g_label, self._g_noise)
         self._g_out = out
         self._graph = graph
         return graph
+
+    def release_graph(self):
+        """Drop the captured graph (and the NCCL / peer-memory work it holds) so the process group can be torn down:
+        reset the graph, drain the device.  The trainer keeps working eagerly afterwards."""
+        if self._graph is not None:
+            torch.cuda.synchronize(self.device)
+            self._graph.reset()
+            self._graph = None
+            self._g_out = None
+            torch.cuda.synchronize(self.device)
 
 
 def _to_device_tree(tree, device):

@@ -203,6 +203,12 @@ int apb_attn_fwd_f32(const float *q, const float *k, const float *v, float *o, f
 int apb_attn_bwd_f32(const float *q, const float *k, const float *v, const float *o, const float *dout,
                      const float *lse, float *dq, float *dk, float *dv, float *delta, int B, int M, int H,
                      int head_dim, apb_stream_t stream);
+/* Same attention for FEW tokens and any head width (the imitator's anchor head: 4 anchors, head_dim 256,
+ * generator_component4_15.py:534-585): M <= 32 tokens, p = (B,H,M,M) soft-max probabilities kept for the backward. */
+int apb_attn_small_fwd_f32(const float *q, const float *k, const float *v, float *o, float *p, int B, int M, int H,
+                           int head_dim, apb_stream_t stream);
+int apb_attn_small_bwd_f32(const float *q, const float *k, const float *v, const float *p, const float *dout,
+                           float *dq, float *dk, float *dv, int B, int M, int H, int head_dim, apb_stream_t stream);
 
 /* ---- small all-reduce over NVLink peer memory (SyncBN statistics) -------------------------------------------
  * Replaces the per-layer collective of torch SyncBatchNorm the reference switches on for world_size > 1

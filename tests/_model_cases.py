@@ -20,6 +20,29 @@ from adaptpoint_b200.synth import make_clouds  # noqa: E402
 # CPU run that produced the goldens, so they are compared at 2e-4 / 2e-3 relative to the tensor's max magnitude.
 TOL_OUT = 2e-4
 TOL_GRAD = 2e-3
+# Second profile: the same cases on the PRODUCT path (conv_backend "tc": TF32 tcgen05 convs + own BatchNorm kernels).
+# TF32 operands round each product at 2^-11; outputs are compared at 5e-3 / 3e-2 (training-mode logits: the head's
+# BatchNorm1d over 2-3 samples amplifies), gradients by direction (cosine) and magnitude.
+PROFILES = {"strict": dict(out=TOL_OUT, out_train=TOL_OUT, grad=TOL_GRAD, loss=1e-4, cos=None),
+            "tc": dict(out=5e-3, out_train=3e-2, grad=None, loss=3e-3, cos=0.99)}
+PROFILE = PROFILES["strict"]
+
+
+def use_profile(name):
+    global PROFILE
+    PROFILE = PROFILES[name]
+
+
+def check_tensor_grad(got, want, name):
+    """fp32 profile: max-abs error relative to the tensor's max; tc profile: direction + norm."""
+    if PROFILE["cos"] is None:
+        e = rel_err(got, want)
+        assert e < PROFILE["grad"], f"{name}: rel err {e:.2e}"
+        return
+    a, b = np.asarray(got, np.float64).ravel(), np.asarray(want, np.float64).ravel()
+    cos = float(a @ b / max(np.linalg.norm(a) * np.linalg.norm(b), 1e-30))
+    nrm = abs(np.linalg.norm(a) / max(np.linalg.norm(b), 1e-30) - 1.0)
+    assert cos > PROFILE["cos"] and nrm < 5e-2, f"{name}: cos {cos:.4f}, norm off by {nrm:.3f}"
 
 
 def strict_fp32():
@@ -57,13 +80,16 @@ def check_names(names, g):
     assert [n for n, _ in names] == list(g["param_names"]), "state_dict names differ from the reference"
 
 
-def check_grads(model, g, tol=TOL_GRAD):
+def check_grads(model, g, tol=None):
     params = dict(model.named_parameters())
     for k in g.files:
         if k.startswith("grad::"):
             got = params[k[6:]].grad.detach().cpu().numpy()
-            e = rel_err(got, g[k])
-            assert e < tol, f"{k}: rel err {e:.2e}"
+            if tol is not None and PROFILE["cos"] is None:
+                e = rel_err(got, g[k])
+                assert e < tol, f"{k}: rel err {e:.2e}"
+            else:
+                check_tensor_grad(got, g[k], k)
 
 
 def case_cls_s(dev, fused=False):
@@ -76,7 +102,7 @@ def case_cls_s(dev, fused=False):
     model.eval()
     with torch.no_grad():
         logits = model({"pos": pos.to(dev), "x": x.to(dev)})
-    tol = 3e-2 if fused else TOL_OUT   # bf16 tensor-core MLP path: north_star tolerance 2e-2 per layer
+    tol = 3e-2 if fused else PROFILE["out"]   # bf16 tensor-core MLP path: north_star tolerance 2e-2 per layer
     e = rel_err(logits.cpu().numpy(), g["logits_eval"])
     assert e < tol, f"eval logits rel err {e:.3e}"
     if fused:
@@ -86,10 +112,11 @@ def case_cls_s(dev, fused=False):
     x_g = x.to(dev).requires_grad_(True)
     logits_tr, loss = model.get_logits_loss({"pos": pos_g, "x": x_g}, y.to(dev))
     loss.backward()
-    assert rel_err(logits_tr.detach().cpu().numpy(), g["logits_train"]) < TOL_OUT
-    assert abs(loss.item() - float(g["loss"])) < 1e-4 * abs(float(g["loss"]))
-    assert rel_err(pos_g.grad.cpu().numpy(), g["grad_pos"]) < TOL_GRAD
-    assert rel_err(x_g.grad.cpu().numpy(), g["grad_x"]) < TOL_GRAD
+    e = rel_err(logits_tr.detach().cpu().numpy(), g["logits_train"])
+    assert e < PROFILE["out_train"], f"train logits rel err {e:.3e}"
+    assert abs(loss.item() - float(g["loss"])) < PROFILE["loss"] * abs(float(g["loss"]))
+    check_tensor_grad(pos_g.grad.cpu().numpy(), g["grad_pos"], "grad_pos")
+    check_tensor_grad(x_g.grad.cpu().numpy(), g["grad_x"], "grad_x")
     check_grads(model, g)
 
 
@@ -103,7 +130,7 @@ def case_seg_b(dev, fused=False):
     model.eval()
     with torch.no_grad():
         out = model({"pos": pos.to(dev), "x": x.to(dev)})
-    tol = 3e-2 if fused else TOL_OUT
+    tol = 3e-2 if fused else PROFILE["out"]
     e = rel_err(out.cpu().numpy(), g["seg_eval"])
     assert e < tol, f"eval seg logits rel err {e:.3e}"
     if fused:
@@ -114,9 +141,10 @@ def case_seg_b(dev, fused=False):
     tgt = torch.randint(0, 13, (int(g["B"]), int(g["N"])), generator=torch.Generator().manual_seed(5)).to(dev)
     loss = torch.nn.functional.cross_entropy(out, tgt)
     loss.backward()
-    assert rel_err(out.detach().cpu().numpy(), g["seg_train"]) < TOL_OUT
-    assert abs(loss.item() - float(g["loss"])) < 1e-4 * abs(float(g["loss"]))
-    assert rel_err(x_g.grad.cpu().numpy(), g["grad_x"]) < TOL_GRAD
+    e = rel_err(out.detach().cpu().numpy(), g["seg_train"])
+    assert e < PROFILE["out_train"], f"train seg logits rel err {e:.3e}"
+    assert abs(loss.item() - float(g["loss"])) < PROFILE["loss"] * abs(float(g["loss"]))
+    check_tensor_grad(x_g.grad.cpu().numpy(), g["grad_x"], "grad_x")
     check_grads(model, g)
 
 
@@ -151,14 +179,23 @@ def case_generator(dev):
     gen.to(dev).train()
     pos, _, _ = batch(int(g["B"]), int(g["N"]), int(g["seed"]))
     noise = _noise(g, ["gumbel", "dropout", "axis", "proj_axis"], dev)
-    _, xyz_new = gen(pos.to(dev), noise=noise)
-    got, want = xyz_new.detach().cpu().numpy(), g["xyz_new"]
-    # a Gumbel-argmax flip on a near-tie logit would zero / un-zero single points: allow none on CPU, <=0.5% on GPU
-    bad = (np.abs(got - want).max(-1) > 1e-4).mean()
+    # (1) own Gumbel arg-max decisions: a flip on a near-tie logit would zero / un-zero single points -- allow none on
+    # the CPU, <= 0.5 % on the GPU (different summation order in front of a tau = 0.1 soft-max)
+    with torch.no_grad():
+        _, xyz_own = gen(pos.to(dev), noise=noise)
+    want = g["xyz_new"]
+    cloud_tol = 1e-4 if PROFILE["cos"] is None else 5e-3
+    bad = (np.abs(xyz_own.cpu().numpy() - want).max(-1) > cloud_tol).mean()
     assert bad <= (0.0 if str(dev) == "cpu" else 0.005), f"{bad:.4f} of the points differ"
+    # (2) the reference run's decisions injected (hard one-hot recovered from its output: masked points are exactly
+    # 0): every point must now agree and the gradient check always runs
+    keep = torch.from_numpy((want != 0).any(-1))
+    noise["hard_mask"] = torch.stack([keep, ~keep], -1).float().to(dev)
+    _, xyz_new = gen(pos.to(dev), noise=noise)
+    bad = (np.abs(xyz_new.detach().cpu().numpy() - want).max(-1) > cloud_tol).mean()
+    assert bad == 0.0, f"{bad:.4f} of the points differ with the reference's mask decisions injected"
     (xyz_new * torch.from_numpy(g["w"]).to(dev)).sum().backward()
-    if bad == 0.0:
-        check_grads(gen, g, tol=5e-3)
+    check_grads(gen, g, tol=5e-3)
 
 
 def case_discriminator(dev):
@@ -171,8 +208,8 @@ def case_discriminator(dev):
     pos_g = pos.to(dev).requires_grad_(True)
     prob = dis(pos_g)
     prob.sum().backward()
-    assert rel_err(prob.detach().cpu().numpy(), g["prob"]) < TOL_OUT
-    assert rel_err(pos_g.grad.cpu().numpy(), g["grad_pos"]) < TOL_GRAD
+    assert rel_err(prob.detach().cpu().numpy(), g["prob"]) < PROFILE["out"]
+    check_tensor_grad(pos_g.grad.cpu().numpy(), g["grad_pos"], "grad_pos")
 
 
 def case_pointwolf(dev):
@@ -183,6 +220,93 @@ def case_pointwolf(dev):
     noise = _noise(g, ["dropout", "axis", "R", "S", "T", "proj_axis"], dev)
     _, out = wolf(pos.to(dev), noise=noise)
     assert rel_err(out.cpu().numpy(), g["out"]) < 2e-5
+
+
+def _cos(a, b):
+    a = np.asarray(a, np.float64).ravel()
+    b = np.asarray(b, np.float64).ravel()
+    return float(a @ b / max(np.linalg.norm(a) * np.linalg.norm(b), 1e-30))
+
+
+# tolerances of the whole-iteration case: strict = fp32 everywhere (CPU stand-in ops, or CUDA with the test-only
+# "torch" conv backend); tc = the benchmarked product path (TF32 tcgen05 1x1 convs fwd/dgrad/wgrad, own BatchNorm /
+# attention / deformation kernels).  TF32 operands carry a 2^-11 relative rounding per product.
+STEP_TOL = {"strict": dict(loss=1e-4, cloud=2e-4, logits=1e-3, gnorm=2e-3, grad=5e-3, cos=0.9999),
+            "tc": dict(loss=3e-3, cloud=5e-3, logits=5e-2, gnorm=3e-2, grad=None, cos=0.99)}
+
+
+def case_step(dev, mode="strict", fused_eval=False, overlap=None):
+    """ONE AdaptPoint iteration (train_gan body + train_one_epoch body) against tests/golden/model_step.npz, which
+    the reference's own generator / discriminator / classifier / get_feedback_loss_ver1 produced
+    (tests/golden/make_step_golden.py): the three losses, the generated cloud, the classifier's training logits, and
+    the gradient norm + selected gradient tensors of each of the three networks."""
+    from adaptpoint_b200 import tcconv
+    from adaptpoint_b200.train import AdaptPointTrainer
+    g = load("step")
+    tol = STEP_TOL[mode]
+    is_cuda = str(dev) != "cpu"
+    kw = {} if overlap is None else {"overlap": overlap}
+    tr = AdaptPointTrainer(device=dev, seed=0, conv_backend="tc" if mode == "tc" else "torch", fused_eval=fused_eval, **kw)
+    fill_state(tr.classifier, 0)
+    fill_state(tr.generator, 2)
+    fill_state(tr.discriminator, 3)
+    for net in (tr.classifier, tr.generator, tr.discriminator):
+        for sub in net.modules():
+            if isinstance(sub, torch.nn.Dropout):
+                sub.p = 0.0
+    B, N = int(g["B"]), int(g["N"])
+    pos = make_clouds(B, N, "shell", int(g["seed"]))
+    h = pos[:, :, 1:2] - pos[:, :, 1:2].amin(dim=1, keepdim=True)
+    points = torch.cat([pos, h], -1).contiguous().to(dev)
+    label = torch.from_numpy(g["label"]).to(dev)
+    mask0 = torch.from_numpy((g["gen_imgs"] != 0).any(-1))
+    noise = {"wolf": {k[5:]: torch.from_numpy(g[k]) for k in g.files if k.startswith("wolf_")},
+             "gen": dict({k[4:]: torch.from_numpy(g[k]) for k in g.files if k.startswith("gen_") and k != "gen_imgs"},
+                         gumbel=torch.from_numpy(g["gumbel"]),
+                         hard_mask=torch.stack([mask0, ~mask0], -1).float()),
+             "keep": torch.from_numpy(g["keep"])}
+    noise = {k: ({kk: vv.to(dev) for kk, vv in v.items()} if isinstance(v, dict) else v.to(dev)) for k, v in noise.items()}
+    got = {}
+
+    def probe(name, module):
+        sq = sum(float(p.grad.double().pow(2).sum()) for p in module.parameters() if p.grad is not None)
+        got[f"gnorm::{name}"] = sq ** 0.5
+        params = dict(module.named_parameters())
+        for k in g.files:
+            if k.startswith(f"grad::{name}::"):
+                got[k] = params[k.split("::", 2)[2]].grad.detach().cpu().numpy().copy()
+
+    tr.grad_probe = probe
+    with tcconv.conv_backend(tr.conv_backend):
+        fake, g_loss, d_loss = tr.gan_iteration(points, label, noise)
+        logits, cls_loss = tr.classifier_iteration(fake, label, noise["keep"])
+    if is_cuda:
+        torch.cuda.synchronize()
+    rel = lambda a, b: abs(float(a) - float(b)) / max(abs(float(b)), 1e-30)
+    report = {"g_loss": rel(g_loss, g["g_loss"]), "d_loss": rel(d_loss, g["d_loss"]), "cls_loss": rel(cls_loss, g["cls_loss"])}
+    gen = fake[:, :, :3].detach().cpu().numpy()
+    bad = float((np.abs(gen - g["gen_imgs"]).max(-1) > tol["cloud"] * np.abs(g["gen_imgs"]).max()).mean())
+    report["cloud_bad_frac"] = bad
+    report["logits"] = rel_err(logits.cpu().numpy(), g["cls_logits"])
+    for k in g.files:
+        if k.startswith("gnorm::"):
+            report[k] = rel(got[k], g[k])
+        elif k.startswith("grad::"):
+            report["cos::" + k[6:]] = _cos(got[k], g[k])
+            report["rel::" + k[6:]] = rel_err(got[k], g[k])
+    print("step parity", mode, {k: (round(v, 6) if isinstance(v, float) else v) for k, v in report.items()})
+    for k in ("g_loss", "d_loss", "cls_loss"):
+        assert report[k] < tol["loss"], (k, report[k])
+    assert bad == 0.0, f"{bad:.4f} of the generated points differ"
+    assert report["logits"] < tol["logits"], report["logits"]
+    for k, v in report.items():
+        if k.startswith("gnorm::"):
+            assert v < tol["gnorm"], (k, v)
+        elif k.startswith("cos::"):
+            assert v > tol["cos"], (k, v)
+        elif k.startswith("rel::") and tol["grad"] is not None:
+            assert v < tol["grad"], (k, v)
+    return report
 
 
 ALL = [case_cls_s, case_seg_b, case_groupers, case_generator, case_discriminator, case_pointwolf]

@@ -18,3 +18,16 @@ def cuda_dev():
     if not torch.cuda.is_available():
         pytest.skip("no CUDA device")
     return torch.device("cuda:0")
+
+
+@pytest.fixture
+def torch_backend_default():
+    """Tests written as "reference = the stock torch layers, candidate = explicit conv_backend('tc')" run with the
+    TEST-ONLY strict backend as the ambient default; the product default is 'tc' (adaptpoint_b200/tcconv.py)."""
+    from adaptpoint_b200 import tcconv
+    prev = tcconv.get_conv_backend()
+    tcconv.set_conv_backend("torch")
+    try:
+        yield
+    finally:
+        tcconv.set_conv_backend(prev)

@@ -4,7 +4,7 @@ Tolerance: 1e-5 relative (fp32 path, north_star) on outputs, 5e-5 on gradients (
 import pytest
 import torch
 
-pytestmark = pytest.mark.gpu
+pytestmark = [pytest.mark.gpu, pytest.mark.usefixtures("torch_backend_default")]
 
 
 def _ref(q, k, v, H):
@@ -34,6 +34,31 @@ def test_self_attention_fwd_bwd(cuda_dev, B, M, H, scale):
     assert _rel(got[0], want[0]) < 1e-5
     for g, w in zip(got[1:], want[1:]):
         assert _rel(g, w) < 5e-5
+
+
+@pytest.mark.parametrize("B,M,H,D", [(32, 4, 4, 256), (2, 32, 2, 40), (3, 1, 4, 7), (2, 17, 3, 100)])
+def test_self_attention_few_tokens_any_head_dim(cuda_dev, B, M, H, D):
+    """apb_attn_small_{fwd,bwd}_f32: the imitator's anchor head (4 anchors, head_dim 256) and other widths."""
+    from adaptpoint_b200 import ops
+    gen = torch.Generator().manual_seed(M * D)
+    q, k, v = [torch.randn(B, M, H * D, generator=gen).to(cuda_dev).requires_grad_(True) for _ in range(3)]
+    go = torch.randn(B, M, H * D, generator=gen).to(cuda_dev)
+    o = ops.self_attention(q, k, v, H)
+    o.backward(go)
+    got = [o.detach(), q.grad.clone(), k.grad.clone(), v.grad.clone()]
+    qd, kd, vd = [t.detach().double().requires_grad_(True) for t in (q, k, v)]
+    od = _ref(qd, kd, vd, H)
+    od.backward(go.double())
+    assert _rel(got[0], od.detach()) < 1e-5
+    for g, w in zip(got[1:], [qd.grad, kd.grad, vd.grad]):
+        assert _rel(g, w) < 5e-5
+
+
+def test_self_attention_outside_kernel_family_raises(cuda_dev):
+    from adaptpoint_b200 import _cabi, ops
+    x = torch.randn(1, 64, 4 * 24, device=cuda_dev)
+    with pytest.raises(_cabi.ApbError):
+        ops.self_attention(x, x, x, 4)
 
 
 def test_anchor_selfattention_module_matches_sdpa(cuda_dev):

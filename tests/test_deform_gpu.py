@@ -10,7 +10,7 @@ from adaptpoint_b200 import imitator
 from adaptpoint_b200.synth import make_clouds
 from oracle import torch_ops
 
-pytestmark = pytest.mark.gpu
+pytestmark = [pytest.mark.gpu, pytest.mark.usefixtures("torch_backend_default")]
 
 
 def _inputs(B, N, M, seed, with_mask):

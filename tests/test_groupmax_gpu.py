@@ -4,7 +4,7 @@ reference formulation (generator_component4_15.py:368-431).  Values are bit-exac
 import pytest
 import torch
 
-pytestmark = pytest.mark.gpu
+pytestmark = [pytest.mark.gpu, pytest.mark.usefixtures("torch_backend_default")]
 
 
 @pytest.mark.parametrize("B,C,N,M,K", [(4, 64, 2048, 1024, 24), (2, 5, 1000, 333, 7), (3, 128, 512, 128, 32),

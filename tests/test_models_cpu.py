@@ -15,6 +15,13 @@ def test_module_parity_cpu(case):
         case("cpu")
 
 
+def test_adaptpoint_iteration_vs_reference_cpu():
+    """One whole AdaptPoint iteration (imitator + discriminator + classifier updates) of OUR trainer on the CPU stand-in
+    ops against the reference's own modules / feedback loss (tests/golden/model_step.npz)."""
+    with torch_ops.patched():
+        mc.case_step("cpu", "strict")
+
+
 def test_trainer_step_cpu():
     from adaptpoint_b200.synth import make_clouds
     with torch_ops.patched():

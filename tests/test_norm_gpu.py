@@ -6,7 +6,7 @@ import pytest
 import torch
 import torch.nn as nn
 
-pytestmark = pytest.mark.gpu
+pytestmark = [pytest.mark.gpu, pytest.mark.usefixtures("torch_backend_default")]
 TOL = 2e-4
 
 
