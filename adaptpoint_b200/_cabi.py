@@ -36,6 +36,9 @@ _SIGNATURES = {
     "apb_deform_mask_bwd_f32": [_p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _i, _i, _i, _p],
     "apb_pwconv_fwd_bf16": [_p, _p, _p, _p, _i, _p, _i, _i, _i, _i, _i, _p],
     "apb_pwconv_fwd_tf32": [_p, _p, _p, _p, _i, _p, _i, _i, _i, _i, _i, _p],
+    "apb_pwconv_fwd_tf32_rows": [_p, _p, _p, _p, _i, _p, _i, _i, _i, _i, _i, _p],
+    "apb_pwconv_ex_tf32": [_p, _p, _p, _p, _i, _p, _i, _p, _p, _i, _i, _i, _i, _i, _p],
+    "apb_pmax_decode": [_p, _p, _p, _ll, _p],
     "apb_pwconv_wgrad_tf32": [_p, _p, _p, _i, _i, _i, _i, _p],
     "apb_affine_f32": [_p, _p, _p, _p, _i, _p, _i, _i, _ll, _p],
     "apb_bn_stats_f32": [_p, _p, _i, _i, _ll, _p],

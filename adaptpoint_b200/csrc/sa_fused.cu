@@ -587,8 +587,11 @@ extern "C" int apb_pwconv_fwd_bf16(const float *x, const uint16_t *w_bf16, const
     return launch_tc<LOAD_CHANNEL_MAJOR, EPI_STORE_CM>(p, w_bf16, Kp, (cudaStream_t)stream);
 }
 
-extern "C" int apb_pwconv_fwd_tf32(const float *x, const float *w, const float *scale, const float *shift, int relu,
-                                   float *y, int B, int Cin, int Cout, int P, int Kp, apb_stream_t stream) {
+// Register-staged TF32 row GEMM (round 1).  apb_pwconv_fwd_tf32 (tc_cm_gemm.cu, both operands by TMA) falls back to it
+// when the activation rows are not 16-byte aligned (P % 4 != 0), which TMA cannot address.
+extern "C" int apb_pwconv_fwd_tf32_rows(const float *x, const float *w, const float *scale, const float *shift,
+                                        int relu, float *y, int B, int Cin, int Cout, int P, int Kp,
+                                        apb_stream_t stream) {
     if (B < 0 || Cin <= 0 || Cout <= 0 || P < 0 || Kp < Cin) return APB_E_INVALID;
     if (B == 0 || P == 0) return APB_OK;
     if (!x || !w || !y || ((scale == nullptr) != (shift == nullptr))) return APB_E_INVALID;

@@ -342,8 +342,9 @@ class AdaptPoint_Augmentor(nn.Module):
         B, N, _ = xyz.shape
         dev = xyz.device
         fps_idx, anchor = geometry.sample(xyz, self.num_anchor)
-        probs, masking = self.predict_prob_layer(xyz, fps_idx, None if noise is None else noise.get("gumbel"),
-                                                 None if noise is None else noise.get("hard_mask"))
+        on_dev = lambda t: None if t is None else t.to(dev)
+        probs, masking = self.predict_prob_layer(xyz, fps_idx, None if noise is None else on_dev(noise.get("gumbel")),
+                                                 None if noise is None else on_dev(noise.get("hard_mask")))
         noise = self.draw(B) if noise is None else noise
         drop, axis = noise["dropout"].to(dev), noise["axis"].to(dev).float()
         degree = math.pi * (torch.tanh(probs[:, :, 0:3]) * self.w_R_range) / 180.0 * drop[:, :, 0:1]

@@ -47,12 +47,15 @@ class BatchNormActFn(Function):
     """y = relu?(BN_batchstats(x)); x (B,C,*) f32 contiguous."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, running_mean, running_var, momentum, eps, relu, group):
+    def forward(ctx, x, weight, bias, running_mean, running_var, momentum, eps, relu, group, stats=None):
+        """stats: (C,2) f64 sum / sum of squares of x when the producing GEMM already accumulated them in its epilogue
+        (tcconv.conv_with_stats); otherwise one read pass computes them here."""
         xs = x.contiguous()
         B, C, P = _dims(xs)
         dev = xs.device
-        stats = torch.zeros((C, 2), dtype=torch.float64, device=dev)
-        _cabi.call("apb_bn_stats_f32", [xs, stats, B, C, P], dev)
+        if stats is None:
+            stats = torch.zeros((C, 2), dtype=torch.float64, device=dev)
+            _cabi.call("apb_bn_stats_f32", [xs, stats, B, C, P], dev)
         world = _allreduce(stats, group)
         count = float(B * P * world)
         y = torch.empty_like(xs)
@@ -80,7 +83,7 @@ class BatchNormActFn(Function):
             _cabi.call("apb_bn_bwd_apply_f32", [xs, g, y, save_mean, save_rstd, weight, stats2, ctx.count, dx, B, C, P],
                        dev)
         # parameter gradients are per-rank sums (the data-parallel all-reduce averages them afterwards)
-        return dx, local[:, 1].float(), local[:, 0].float(), None, None, None, None, None, None
+        return dx, local[:, 1].float(), local[:, 0].float(), None, None, None, None, None, None, None
 
 
 class BatchNormEvalFn(Function):
@@ -195,11 +198,12 @@ def _tc_ok(bn, x):
 class _TcBatchNormMixin:
     process_group = None  # set by enable_sync(): SyncBatchNorm semantics over that group
 
-    def forward_act(self, x, relu):
-        """BatchNorm (+ReLU when `relu`) -- fused kernels in training mode on the tc backend, torch otherwise."""
+    def forward_act(self, x, relu, stats=None):
+        """BatchNorm (+ReLU when `relu`) -- fused kernels in training mode on the tc backend, torch otherwise.
+        `stats`: batch statistics of x already accumulated by the producing GEMM (see BatchNormActFn)."""
         if self.training and _tc_ok(self, x):
             y = BatchNormActFn.apply(x, self.weight, self.bias, self.running_mean, self.running_var, self.momentum,
-                                     self.eps, relu, self.process_group)
+                                     self.eps, relu, self.process_group, stats)
             self.num_batches_tracked.add_(1)
             return y
         if not self.training and _tc_ok(self, x):
@@ -240,13 +244,21 @@ class ConvBlock(nn.Sequential):
     def forward(self, x):
         mods = list(self)
         i = 0
+        stats = None
         while i < len(mods):
             m = mods[i]
-            if (isinstance(m, _TcBatchNormMixin) and i + 1 < len(mods) and isinstance(mods[i + 1], nn.ReLU)):
-                x = m.forward_act(x, True)
-                i += 2
+            if isinstance(m, _TcBatchNormMixin):
+                relu = i + 1 < len(mods) and isinstance(mods[i + 1], nn.ReLU)
+                x = m.forward_act(x, relu, stats)
+                stats = None
+                i += 2 if relu else 1
                 continue
-            x = m(x)
+            nxt = mods[i + 1] if i + 1 < len(mods) else None
+            if (isinstance(m, (tcconv.TcConv1d, tcconv.TcConv2d)) and isinstance(nxt, _TcBatchNormMixin)
+                    and nxt.training and _tc_ok(nxt, x)):
+                x, stats = tcconv.conv_with_stats(m, x)   # statistics of the conv output from the GEMM epilogue
+            else:
+                x = m(x)
             i += 1
         return x
 

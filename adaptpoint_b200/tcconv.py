@@ -74,8 +74,26 @@ def pack_f32(W):
     return out, kp
 
 
-def _gemm_rows(x, w2d, bias, B, cin, cout, P):
-    """y (B,cout,P) = w2d (cout,cin) . x (B,cin,P) (+bias) through apb_pwconv_fwd_{tf32,bf16}, splitting cout > 512."""
+def tma_ok(x, P):
+    """The TMA-fed TF32 kernel (csrc/tc_cm_gemm.cu) addresses rows of P floats: 16-byte aligned rows only."""
+    return _PRECISION == "tf32" and P % 4 == 0 and x.data_ptr() % 16 == 0
+
+
+def _gemm_rows(x, w2d, bias, B, cin, cout, P, stats=None):
+    """y (B,cout,P) = w2d (cout,cin) . x (B,cin,P) (+bias) through apb_pwconv_fwd_{tf32,bf16}.  The TMA-fed TF32 kernel
+    takes any cout in one launch (and can accumulate the BatchNorm statistics of y into `stats` (cout,2) f64); the
+    register-staged kernels are called in slices of <= 512 output channels."""
+    if tma_ok(x, P):
+        wb, kp = pack_f32(w2d)
+        y = torch.empty((B, cout, P), dtype=torch.float32, device=x.device)
+        shift = None if bias is None else bias.contiguous().float()
+        if stats is None:
+            _cabi.call("apb_pwconv_fwd_tf32", [x, wb, None, shift, 0, y, B, cin, cout, P, kp], x.device)
+        else:
+            _cabi.call("apb_pwconv_ex_tf32", [x, wb, None, shift, 0, y, 0, stats, None, B, cin, cout, P, kp], x.device)
+        return y
+    if stats is not None:
+        raise _cabi.ApbError("fused BatchNorm statistics need the TMA-fed kernel (P % 4 == 0)")
     outs = []
     entry = "apb_pwconv_fwd_tf32" if _PRECISION == "tf32" else "apb_pwconv_fwd_bf16"
     for c0 in range(0, cout, _MAX_N):
@@ -94,7 +112,9 @@ def _gemm_rows(x, w2d, bias, B, cin, cout, P):
 
 class PointwiseConvFn(Function):
     @staticmethod
-    def forward(ctx, x, weight, bias):
+    def forward(ctx, x, weight, bias, stats=None):
+        """stats: optional pre-zeroed (Cout,2) f64 tensor that receives sum / sum of squares of the output (the batch
+        statistics of a BatchNorm that follows), accumulated in the GEMM epilogue."""
         shp = x.shape
         B, cin = shp[0], shp[1]
         P = 1
@@ -103,7 +123,7 @@ class PointwiseConvFn(Function):
         cout = weight.shape[0]
         xs = x.detach().contiguous().float()
         w2d = weight.detach().reshape(cout, cin).float()
-        y = _gemm_rows(xs, w2d, None if bias is None else bias.detach(), B, cin, cout, P)
+        y = _gemm_rows(xs, w2d, None if bias is None else bias.detach(), B, cin, cout, P, stats)
         ctx.save_for_backward(xs, weight)
         ctx.has_bias = bias is not None
         ctx.dims = (B, cin, cout, P, tuple(shp))
@@ -127,14 +147,15 @@ class PointwiseConvFn(Function):
             gw = gw.view(weight.shape)
         if ctx.has_bias and ctx.needs_input_grad[2]:
             gb = g.sum(dim=(0, 2))
-        return gx, gw, gb
+        return gx, gw, gb, None
 
 
 class PointwiseConvMaxFn(Function):
-    """pooled (B,Cout) = max over the points of (W x + b), x (B,Cin,P): the 1x1 conv runs on the tensor cores in
-    slices of <= 512 output channels, each slice is reduced by apb_rowmax_f32 and dropped, so the (B,Cout,P)
-    activation is never concatenated, ReLU'd or re-read; the backward pass touches only the arg-max columns.
-    Callers apply ReLU to the pooled result (max(relu(y)) == relu(max(y)))."""
+    """pooled (B,Cout) = max over the points of (W x + b), x (B,Cin,P).  On the TMA-fed TF32 kernel the max and its
+    first arg-max are taken in the GEMM epilogue (apb_pwconv_ex_tf32 with `pmax`): the (B,Cout,P) activation is never
+    written.  Shapes TMA cannot address (P % 4 != 0) run the conv in slices of <= 512 output channels, each reduced by
+    apb_rowmax_f32 and dropped.  The backward pass touches only the arg-max columns.  Callers apply ReLU to the pooled
+    result (max(relu(y)) == relu(max(y)))."""
 
     @staticmethod
     def forward(ctx, x, weight, bias):
@@ -143,6 +164,19 @@ class PointwiseConvMaxFn(Function):
         cout = weight.shape[0]
         xs = x.detach().contiguous().float().view(B, cin, P)
         w2d = weight.detach().reshape(cout, cin).float()
+        if tma_ok(xs, P):
+            wb, kp = pack_f32(w2d)
+            packed = torch.zeros((B, cout), dtype=torch.int64, device=x.device)
+            shift = None if bias is None else bias.detach().contiguous().float()
+            _cabi.call("apb_pwconv_ex_tf32", [xs, wb, None, shift, 0, None, 0, None, packed, B, cin, cout, P, kp],
+                       x.device)
+            val = torch.empty((B, cout), dtype=torch.float32, device=x.device)
+            arg32 = torch.empty((B, cout), dtype=torch.int32, device=x.device)
+            _cabi.call("apb_pmax_decode", [packed, val, arg32, B * cout], x.device)
+            ctx.save_for_backward(xs, weight, arg32.long())
+            ctx.has_bias = bias is not None
+            ctx.xshape = tuple(x.shape)
+            return val
         vals, args = [], []
         for c0 in range(0, cout, _MAX_N):
             c1 = min(cout, c0 + _MAX_N)
@@ -192,6 +226,17 @@ def _use_tc(mod, x):
     return (_BACKEND == "tc" and x.is_cuda and x.dtype == torch.float32 and mod.groups == 1
             and all(k == 1 for k in mod.kernel_size) and all(s == 1 for s in mod.stride)
             and all(p == 0 for p in mod.padding))
+
+
+def conv_with_stats(mod, x):
+    """(y, stats): y = mod(x) and, when the TMA-fed kernel can run this shape, stats (Cout,2) f64 = sum / sum of
+    squares of y over (batch, positions) from the GEMM epilogue; stats is None otherwise (caller runs its own pass)."""
+    if _use_tc(mod, x):
+        P = x[0, 0].numel()
+        if _PRECISION == "tf32" and P % 4 == 0:
+            stats = torch.zeros((mod.out_channels, 2), dtype=torch.float64, device=x.device)
+            return PointwiseConvFn.apply(x, mod.weight, mod.bias, stats), stats
+    return mod(x), None
 
 
 class TcConv1d(nn.Conv1d):

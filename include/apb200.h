@@ -131,11 +131,29 @@ int apb_deform_mask_bwd_f32(const float *xyz, const float *anchor, const float *
 int apb_pwconv_fwd_bf16(const float *x, const uint16_t *w_bf16, const float *scale, const float *shift, int relu,
                         float *y, int B, int Cin, int Cout, int P, int Kp, apb_stream_t stream);
 
-/* Same layer with TF32 operands (fp32 inputs rounded to tf32 by the producers / the TMA unit, fp32 accumulate):
- *   w (Cout,Kp) f32 K-major, columns >= Cin zero, Kp % 32 == 0.  This is the training-path precision: it equals the
- * reference's default cuDNN behaviour on Ampere+ (torch.backends.cudnn.allow_tf32 = True). */
+/* Same layer with TF32 operands (fp32 inputs read as tf32 by the TMA unit, fp32 accumulate):
+ *   w (Cout,Kp) f32 K-major, columns >= Cin zero, Kp % 32 == 0; any Cout.  This is the training-path precision: it
+ * equals the reference's default cuDNN behaviour on Ampere+ (torch.backends.cudnn.allow_tf32 = True).
+ * Both operands go global -> shared memory by TMA (csrc/tc_cm_gemm.cu: the channel-major activation is the MN-major
+ * operand of tcgen05.mma, no thread touches it); needs P % 4 == 0 and 16-byte aligned x, w -- other shapes take the
+ * register-staged kernel apb_pwconv_fwd_tf32_rows (Cout <= 512). */
 int apb_pwconv_fwd_tf32(const float *x, const float *w, const float *scale, const float *shift, int relu, float *y,
                         int B, int Cin, int Cout, int P, int Kp, apb_stream_t stream);
+int apb_pwconv_fwd_tf32_rows(const float *x, const float *w, const float *scale, const float *shift, int relu, float *y,
+                             int B, int Cin, int Cout, int P, int Kp, apb_stream_t stream);
+/* The TMA-fed kernel with its epilogue variants (APB_E_UNSUPPORTED unless P % 4 == 0 and x, w 16-byte aligned):
+ *   point_major != 0 : y is (B*P, Cout) row-major (the per-support-point operand U of the fused set abstraction);
+ *   stats != NULL    : (Cout,2) f64, += sum and sum of squares over (b,p) of scale*(W.x)+shift BEFORE the ReLU -- the
+ *                      batch statistics of the BatchNorm that follows the conv (openpoints/models/layers/norm.py:57-71),
+ *                      so no separate statistics pass reads y again;
+ *   pmax != NULL     : (B,Cout) u64 pre-zeroed; y is not written; pmax[b,c] = max over p of scale*(W.x)+shift packed
+ *                      as (order-preserving value bits << 32 | 0xFFFFFFFF - first arg-max p): the conv -> ReLU -> max
+ *                      over the points head of the discriminator (point_discriminator.py:166-191) without the
+ *                      (B,Cout,P) activation.  apb_pmax_decode unpacks n entries into value / arg. */
+int apb_pwconv_ex_tf32(const float *x, const float *w, const float *scale, const float *shift, int relu, float *y,
+                       int point_major, double *stats, unsigned long long *pmax, int B, int Cin, int Cout, int P,
+                       int Kp, apb_stream_t stream);
+int apb_pmax_decode(const unsigned long long *packed, float *val, int32_t *arg, long long n, apb_stream_t stream);
 
 /* Weight gradient of the 1x1 convolution above (TF32 tcgen05, both operands TMA-fed):
  *   grad_w[co,ci] += sum_{b,p} grad_y[b,co,p] * x[b,ci,p];  grad_w (Cout,Cin) f32 pre-zeroed by the caller.

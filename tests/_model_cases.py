@@ -20,29 +20,59 @@ from adaptpoint_b200.synth import make_clouds  # noqa: E402
 # CPU run that produced the goldens, so they are compared at 2e-4 / 2e-3 relative to the tensor's max magnitude.
 TOL_OUT = 2e-4
 TOL_GRAD = 2e-3
-# Second profile: the same cases on the PRODUCT path (conv_backend "tc": TF32 tcgen05 convs + own BatchNorm kernels).
-# TF32 operands round each product at 2^-11; outputs are compared at 5e-3 / 3e-2 (training-mode logits: the head's
-# BatchNorm1d over 2-3 samples amplifies), gradients by direction (cosine) and magnitude.
-PROFILES = {"strict": dict(out=TOL_OUT, out_train=TOL_OUT, grad=TOL_GRAD, loss=1e-4, cos=None),
-            "tc": dict(out=5e-3, out_train=3e-2, grad=None, loss=3e-3, cos=0.99)}
-PROFILE = PROFILES["strict"]
+# ---------------------------------------------------------------------------------------------------------------
+# How a compared quantity is judged.  Every case funnels its comparisons through check(kind, name, value[, limit]):
+#   "strict"   : value <= the fp32 limit of its kind (CPU stand-in ops, or CUDA with the TEST-ONLY "torch" backend and
+#                library TF32 switched off);
+#   "record"   : remember the value -- used for a run of the stock torch layers at the REFERENCE'S DEFAULT PRECISION
+#                (cuDNN convolutions with TF32 allowed, torch.backends.cudnn.allow_tf32 = True);
+#   "relative" : the PRODUCT path (conv_backend "tc": TF32 tcgen05 convs fwd/dgrad/wgrad + own BatchNorm, attention,
+#                deformation kernels) must deviate from the fp32 golden by no more than K x what cuDNN-TF32 deviated
+#                (same fixture, same device), or the TF32 floor of its kind, whichever is larger.
+# The relative form is needed because the fixtures carry training-mode BatchNorm over 2-4 samples in the heads, which
+# amplifies ANY operand rounding by 10^2-10^3 (the strict CUDA run already shows 1e-7 -> 4e-5): an absolute TF32
+# tolerance on those quantities would measure the fixture's conditioning, not the kernels.
+# ---------------------------------------------------------------------------------------------------------------
+STRICT = dict(out=TOL_OUT, out_train=TOL_OUT, loss=1e-4, gradrel=TOL_GRAD, cos=1e-3, nrm=2e-2, frac=0.0)
+FLOOR = dict(out=5e-3, out_train=5e-3, loss=3e-3, gradrel=float("inf"), cos=1e-2, nrm=5e-2, frac=0.005)
+_JUDGE = {"mode": "strict", "rec": {}, "K": 3.0, "log": []}
 
 
-def use_profile(name):
-    global PROFILE
-    PROFILE = PROFILES[name]
+def begin(mode):
+    """'strict' | 'record' | 'relative' (see above); returns the log of (kind, name, value, limit)."""
+    _JUDGE["mode"] = mode
+    if mode == "record":
+        _JUDGE["rec"] = {}
+    _JUDGE["log"] = []
+    return _JUDGE["log"]
 
 
-def check_tensor_grad(got, want, name):
-    """fp32 profile: max-abs error relative to the tensor's max; tc profile: direction + norm."""
-    if PROFILE["cos"] is None:
-        e = rel_err(got, want)
-        assert e < PROFILE["grad"], f"{name}: rel err {e:.2e}"
+def check(kind, name, value, limit=None):
+    value = float(value)
+    mode = _JUDGE["mode"]
+    if mode == "record":
+        _JUDGE["rec"][name] = value
+        _JUDGE["log"].append((kind, name, value, None))
         return
+    if mode == "strict":
+        lim = STRICT[kind] if limit is None else limit
+        what = "fp32 limit"
+    else:
+        ref = _JUDGE["rec"].get(name)
+        assert ref is not None, f"{name}: no cuDNN-TF32 record to compare with"
+        lim = max(_JUDGE["K"] * ref, FLOOR[kind])
+        what = f"max({_JUDGE['K']:g} x cuDNN-TF32 {ref:.3e}, floor {FLOOR[kind]:g})"
+    _JUDGE["log"].append((kind, name, value, lim))
+    assert value <= lim, f"{name} [{kind}]: {value:.3e} > {what}"
+
+
+def check_tensor_grad(got, want, name, limit=None):
+    """Gradient tensors: max-abs error relative to the tensor's max (fp32 profile), direction and norm (all profiles)."""
     a, b = np.asarray(got, np.float64).ravel(), np.asarray(want, np.float64).ravel()
     cos = float(a @ b / max(np.linalg.norm(a) * np.linalg.norm(b), 1e-30))
-    nrm = abs(np.linalg.norm(a) / max(np.linalg.norm(b), 1e-30) - 1.0)
-    assert cos > PROFILE["cos"] and nrm < 5e-2, f"{name}: cos {cos:.4f}, norm off by {nrm:.3f}"
+    check("gradrel", name + " (rel)", rel_err(got, want), limit)
+    check("cos", name + " (1-cos)", 1.0 - cos)
+    check("nrm", name + " (norm)", abs(np.linalg.norm(a) / max(np.linalg.norm(b), 1e-30) - 1.0))
 
 
 def strict_fp32():
@@ -84,12 +114,7 @@ def check_grads(model, g, tol=None):
     params = dict(model.named_parameters())
     for k in g.files:
         if k.startswith("grad::"):
-            got = params[k[6:]].grad.detach().cpu().numpy()
-            if tol is not None and PROFILE["cos"] is None:
-                e = rel_err(got, g[k])
-                assert e < tol, f"{k}: rel err {e:.2e}"
-            else:
-                check_tensor_grad(got, g[k], k)
+            check_tensor_grad(params[k[6:]].grad.detach().cpu().numpy(), g[k], k, tol)
 
 
 def case_cls_s(dev, fused=False):
@@ -102,9 +127,8 @@ def case_cls_s(dev, fused=False):
     model.eval()
     with torch.no_grad():
         logits = model({"pos": pos.to(dev), "x": x.to(dev)})
-    tol = 3e-2 if fused else PROFILE["out"]   # bf16 tensor-core MLP path: north_star tolerance 2e-2 per layer
-    e = rel_err(logits.cpu().numpy(), g["logits_eval"])
-    assert e < tol, f"eval logits rel err {e:.3e}"
+    # fused: bf16 tensor-core MLP path, north_star tolerance 2e-2 per layer
+    check("out", "eval logits", rel_err(logits.cpu().numpy(), g["logits_eval"]), 3e-2 if fused else None)
     if fused:
         return
     train_no_dropout(model)
@@ -112,9 +136,8 @@ def case_cls_s(dev, fused=False):
     x_g = x.to(dev).requires_grad_(True)
     logits_tr, loss = model.get_logits_loss({"pos": pos_g, "x": x_g}, y.to(dev))
     loss.backward()
-    e = rel_err(logits_tr.detach().cpu().numpy(), g["logits_train"])
-    assert e < PROFILE["out_train"], f"train logits rel err {e:.3e}"
-    assert abs(loss.item() - float(g["loss"])) < PROFILE["loss"] * abs(float(g["loss"]))
+    check("out_train", "train logits", rel_err(logits_tr.detach().cpu().numpy(), g["logits_train"]))
+    check("loss", "loss", abs(loss.item() - float(g["loss"])) / abs(float(g["loss"])))
     check_tensor_grad(pos_g.grad.cpu().numpy(), g["grad_pos"], "grad_pos")
     check_tensor_grad(x_g.grad.cpu().numpy(), g["grad_x"], "grad_x")
     check_grads(model, g)
@@ -130,9 +153,7 @@ def case_seg_b(dev, fused=False):
     model.eval()
     with torch.no_grad():
         out = model({"pos": pos.to(dev), "x": x.to(dev)})
-    tol = 3e-2 if fused else PROFILE["out"]
-    e = rel_err(out.cpu().numpy(), g["seg_eval"])
-    assert e < tol, f"eval seg logits rel err {e:.3e}"
+    check("out", "eval seg logits", rel_err(out.cpu().numpy(), g["seg_eval"]), 3e-2 if fused else None)
     if fused:
         return
     train_no_dropout(model)
@@ -141,9 +162,8 @@ def case_seg_b(dev, fused=False):
     tgt = torch.randint(0, 13, (int(g["B"]), int(g["N"])), generator=torch.Generator().manual_seed(5)).to(dev)
     loss = torch.nn.functional.cross_entropy(out, tgt)
     loss.backward()
-    e = rel_err(out.detach().cpu().numpy(), g["seg_train"])
-    assert e < PROFILE["out_train"], f"train seg logits rel err {e:.3e}"
-    assert abs(loss.item() - float(g["loss"])) < PROFILE["loss"] * abs(float(g["loss"]))
+    check("out_train", "train seg logits", rel_err(out.detach().cpu().numpy(), g["seg_train"]))
+    check("loss", "loss", abs(loss.item() - float(g["loss"])) / abs(float(g["loss"])))
     check_tensor_grad(x_g.grad.cpu().numpy(), g["grad_x"], "grad_x")
     check_grads(model, g)
 
@@ -184,16 +204,16 @@ def case_generator(dev):
     with torch.no_grad():
         _, xyz_own = gen(pos.to(dev), noise=noise)
     want = g["xyz_new"]
-    cloud_tol = 1e-4 if PROFILE["cos"] is None else 5e-3
+    cloud_tol = 1e-4 if _JUDGE["mode"] == "strict" else 5e-3
     bad = (np.abs(xyz_own.cpu().numpy() - want).max(-1) > cloud_tol).mean()
-    assert bad <= (0.0 if str(dev) == "cpu" else 0.005), f"{bad:.4f} of the points differ"
+    check("frac", "points off with own mask decisions", bad, 0.0 if str(dev) == "cpu" else 0.005)
     # (2) the reference run's decisions injected (hard one-hot recovered from its output: masked points are exactly
     # 0): every point must now agree and the gradient check always runs
     keep = torch.from_numpy((want != 0).any(-1))
     noise["hard_mask"] = torch.stack([keep, ~keep], -1).float().to(dev)
     _, xyz_new = gen(pos.to(dev), noise=noise)
     bad = (np.abs(xyz_new.detach().cpu().numpy() - want).max(-1) > cloud_tol).mean()
-    assert bad == 0.0, f"{bad:.4f} of the points differ with the reference's mask decisions injected"
+    check("frac", "points off with the reference's mask decisions injected", bad)
     (xyz_new * torch.from_numpy(g["w"]).to(dev)).sum().backward()
     check_grads(gen, g, tol=5e-3)
 
@@ -203,12 +223,19 @@ def case_discriminator(dev):
     g = load("discriminator")
     dis = PointDiscriminator1(num_classes=15, normal_channel=False)
     check_names(fill_state(dis, 3), g)
-    dis.to(dev).eval()
+    dis.to(dev).train()
+    for sub in dis.modules():
+        if isinstance(sub, torch.nn.Dropout):
+            sub.p = 0.0
     pos, _, _ = batch(2, 512, int(g["seed"]))
+    with torch.no_grad():                 # the golden's warm-up: 5 power iterations of the spectral norms
+        for _ in range(5):
+            dis(pos.to(dev))
+    dis.eval()
     pos_g = pos.to(dev).requires_grad_(True)
     prob = dis(pos_g)
     prob.sum().backward()
-    assert rel_err(prob.detach().cpu().numpy(), g["prob"]) < PROFILE["out"]
+    check("out", "prob", rel_err(prob.detach().cpu().numpy(), g["prob"]))
     check_tensor_grad(pos_g.grad.cpu().numpy(), g["grad_pos"], "grad_pos")
 
 
@@ -222,20 +249,7 @@ def case_pointwolf(dev):
     assert rel_err(out.cpu().numpy(), g["out"]) < 2e-5
 
 
-def _cos(a, b):
-    a = np.asarray(a, np.float64).ravel()
-    b = np.asarray(b, np.float64).ravel()
-    return float(a @ b / max(np.linalg.norm(a) * np.linalg.norm(b), 1e-30))
-
-
-# tolerances of the whole-iteration case: strict = fp32 everywhere (CPU stand-in ops, or CUDA with the test-only
-# "torch" conv backend); tc = the benchmarked product path (TF32 tcgen05 1x1 convs fwd/dgrad/wgrad, own BatchNorm /
-# attention / deformation kernels).  TF32 operands carry a 2^-11 relative rounding per product.
-STEP_TOL = {"strict": dict(loss=1e-4, cloud=2e-4, logits=1e-3, gnorm=2e-3, grad=5e-3, cos=0.9999),
-            "tc": dict(loss=3e-3, cloud=5e-3, logits=5e-2, gnorm=3e-2, grad=None, cos=0.99)}
-
-
-def case_step(dev, mode="strict", fused_eval=False, overlap=None):
+def case_step(dev, backend="torch", fused_eval=False, overlap=None):
     """ONE AdaptPoint iteration (train_gan body + train_one_epoch body) against tests/golden/model_step.npz, which
     the reference's own generator / discriminator / classifier / get_feedback_loss_ver1 produced
     (tests/golden/make_step_golden.py): the three losses, the generated cloud, the classifier's training logits, and
@@ -243,10 +257,9 @@ def case_step(dev, mode="strict", fused_eval=False, overlap=None):
     from adaptpoint_b200 import tcconv
     from adaptpoint_b200.train import AdaptPointTrainer
     g = load("step")
-    tol = STEP_TOL[mode]
     is_cuda = str(dev) != "cpu"
     kw = {} if overlap is None else {"overlap": overlap}
-    tr = AdaptPointTrainer(device=dev, seed=0, conv_backend="tc" if mode == "tc" else "torch", fused_eval=fused_eval, **kw)
+    tr = AdaptPointTrainer(device=dev, seed=0, conv_backend=backend, fused_eval=fused_eval, **kw)
     fill_state(tr.classifier, 0)
     fill_state(tr.generator, 2)
     fill_state(tr.discriminator, 3)
@@ -283,30 +296,17 @@ def case_step(dev, mode="strict", fused_eval=False, overlap=None):
     if is_cuda:
         torch.cuda.synchronize()
     rel = lambda a, b: abs(float(a) - float(b)) / max(abs(float(b)), 1e-30)
-    report = {"g_loss": rel(g_loss, g["g_loss"]), "d_loss": rel(d_loss, g["d_loss"]), "cls_loss": rel(cls_loss, g["cls_loss"])}
+    for name, val in (("g_loss", g_loss), ("d_loss", d_loss), ("cls_loss", cls_loss)):
+        check("loss", name, rel(val, g[name]))
     gen = fake[:, :, :3].detach().cpu().numpy()
-    bad = float((np.abs(gen - g["gen_imgs"]).max(-1) > tol["cloud"] * np.abs(g["gen_imgs"]).max()).mean())
-    report["cloud_bad_frac"] = bad
-    report["logits"] = rel_err(logits.cpu().numpy(), g["cls_logits"])
+    cloud_tol = 2e-4 if _JUDGE["mode"] == "strict" else 5e-3
+    check("frac", "generated points off", float((np.abs(gen - g["gen_imgs"]).max(-1) > cloud_tol * np.abs(g["gen_imgs"]).max()).mean()))
+    check("out_train", "classifier training logits", rel_err(logits.cpu().numpy(), g["cls_logits"]), 1e-3)
     for k in g.files:
         if k.startswith("gnorm::"):
-            report[k] = rel(got[k], g[k])
+            check("nrm", k, rel(got[k], g[k]), 2e-3)
         elif k.startswith("grad::"):
-            report["cos::" + k[6:]] = _cos(got[k], g[k])
-            report["rel::" + k[6:]] = rel_err(got[k], g[k])
-    print("step parity", mode, {k: (round(v, 6) if isinstance(v, float) else v) for k, v in report.items()})
-    for k in ("g_loss", "d_loss", "cls_loss"):
-        assert report[k] < tol["loss"], (k, report[k])
-    assert bad == 0.0, f"{bad:.4f} of the generated points differ"
-    assert report["logits"] < tol["logits"], report["logits"]
-    for k, v in report.items():
-        if k.startswith("gnorm::"):
-            assert v < tol["gnorm"], (k, v)
-        elif k.startswith("cos::"):
-            assert v > tol["cos"], (k, v)
-        elif k.startswith("rel::") and tol["grad"] is not None:
-            assert v < tol["grad"], (k, v)
-    return report
+            check_tensor_grad(got[k], g[k], k, 5e-3)
 
 
 ALL = [case_cls_s, case_seg_b, case_groupers, case_generator, case_discriminator, case_pointwolf]

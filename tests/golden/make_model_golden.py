@@ -132,12 +132,23 @@ def main():
          param_names=np.array([n for n, _ in names]), **grads_summary(gen, gnames))
 
     # ---- discriminator (eval: no dropout, no power iteration) ---------------------------------------------
+    # fill_state draws the spectral-norm vectors u, v at random, which makes sigma = u^T W v arbitrary (round 1's
+    # fixture saturated the sigmoid: prob == 0, gradient == 0).  A few training-mode forwards run the reference's own
+    # power iteration first, so the eval pass below sees converged u, v; the test replays the same warm-up.
     dis = R.PointDiscriminator1(num_classes=15, normal_channel=False)
     names = fill_state(dis, 3)
+    dis.train()
+    for sub in dis.modules():
+        if isinstance(sub, torch.nn.Dropout):
+            sub.p = 0.0
+    with torch.no_grad():
+        for _ in range(5):
+            dis(pos)
     dis.eval()
     pos_g = pos.clone().requires_grad_(True)
     prob = dis(pos_g)
     prob.sum().backward()
+    assert 0.02 < float(prob.min()) and float(prob.max()) < 0.98 and float(pos_g.grad.abs().max()) > 1e-6, prob
     save("discriminator", seed=14, prob=prob.detach().numpy(), grad_pos=pos_g.grad.numpy(),
          param_names=np.array([n for n, _ in names]))
 

@@ -12,6 +12,7 @@ from oracle import torch_ops
 @pytest.mark.parametrize("case", mc.ALL, ids=lambda f: f.__name__)
 def test_module_parity_cpu(case):
     with torch_ops.patched():
+        mc.begin("strict")
         case("cpu")
 
 
@@ -19,7 +20,8 @@ def test_adaptpoint_iteration_vs_reference_cpu():
     """One whole AdaptPoint iteration (imitator + discriminator + classifier updates) of OUR trainer on the CPU stand-in
     ops against the reference's own modules / feedback loss (tests/golden/model_step.npz)."""
     with torch_ops.patched():
-        mc.case_step("cpu", "strict")
+        mc.begin("strict")
+        mc.case_step("cpu", "torch")
 
 
 def test_trainer_step_cpu():

@@ -140,3 +140,76 @@ def test_rowmax_exact(cuda_dev):
         first = (y == want_v[:, None]).float().argmax(dim=1)
         assert torch.equal(v, want_v)
         assert torch.equal(a.long(), first)
+
+
+@pytest.mark.parametrize("B,cin,cout,P", [(32, 128, 512, 2048), (4, 35, 32, 16384), (2, 3, 64, 512), (3, 259, 256, 2048),
+                                          (2, 64, 1024, 1000), (5, 96, 40, 132), (1, 515, 72, 4), (2, 16, 272, 8196)])
+def test_tma_gemm_store_stats_pointmajor(cuda_dev, B, cin, cout, P):
+    """csrc/tc_cm_gemm.cu (both operands by TMA, MN-major activation tile): channel-major store + fused BatchNorm
+    statistics, and the point-major store, against a float64 contraction (TF32 operands: 3e-3)."""
+    from adaptpoint_b200 import _cabi, tcconv
+    gen = torch.Generator().manual_seed(cin * 7 + cout)
+    x = torch.randn(B, cin, P, generator=gen).to(cuda_dev)
+    w = (torch.randn(cout, cin, generator=gen) / cin ** 0.5).to(cuda_dev)
+    bias = torch.randn(cout, generator=gen).to(cuda_dev)
+    wb, kp = tcconv.pack_f32(w)
+    want = torch.einsum("oi,bip->bop", w.double(), x.double()) + bias.double().view(1, cout, 1)
+    y = torch.empty(B, cout, P, device=cuda_dev)
+    stats = torch.zeros(cout, 2, dtype=torch.float64, device=cuda_dev)
+    _cabi.call("apb_pwconv_ex_tf32", [x, wb, None, bias, 1, y, 0, stats, None, B, cin, cout, P, kp], cuda_dev)
+    assert _rel(y, want.clamp_min(0).float()) < 3e-3
+    n = B * P
+    mean_w, sq_w = want.sum(dim=(0, 2)) / n, (want * want).sum(dim=(0, 2)) / n
+    assert ((stats[:, 0] / n - mean_w).abs().max() / mean_w.abs().max()).item() < 2e-3      # statistics are pre-ReLU
+    assert ((stats[:, 1] / n - sq_w).abs().max() / sq_w.abs().max()).item() < 2e-3
+    ypm = torch.empty(B * P, cout, device=cuda_dev)
+    _cabi.call("apb_pwconv_ex_tf32", [x, wb, None, None, 0, ypm, 1, None, None, B, cin, cout, P, kp], cuda_dev)
+    want_pm = (want - bias.double().view(1, cout, 1)).permute(0, 2, 1).reshape(B * P, cout).float()
+    assert _rel(ypm, want_pm) < 3e-3
+
+
+@pytest.mark.parametrize("B,cin,cout,P", [(32, 128, 1024, 2048), (3, 64, 96, 1000), (2, 3, 64, 100), (4, 128, 300, 388)])
+def test_tma_gemm_max_over_points_exact(cuda_dev, B, cin, cout, P):
+    """The max / first-arg-max epilogue must agree EXACTLY with a max over the activation the store epilogue of the same
+    kernel writes (same MMA order => same bits)."""
+    from adaptpoint_b200 import _cabi, tcconv
+    gen = torch.Generator().manual_seed(P + cout)
+    x = torch.randn(B, cin, P, generator=gen).to(cuda_dev)
+    x[:, :, P // 2:] = x[:, :, :P - P // 2]                      # duplicated points: exact ties, first index must win
+    w = (torch.randn(cout, cin, generator=gen) / cin ** 0.5).to(cuda_dev)
+    bias = torch.randn(cout, generator=gen).to(cuda_dev)
+    wb, kp = tcconv.pack_f32(w)
+    y = torch.empty(B, cout, P, device=cuda_dev)
+    _cabi.call("apb_pwconv_fwd_tf32", [x, wb, None, bias, 0, y, B, cin, cout, P, kp], cuda_dev)
+    packed = torch.zeros(B, cout, dtype=torch.int64, device=cuda_dev)
+    _cabi.call("apb_pwconv_ex_tf32", [x, wb, None, bias, 0, None, 0, None, packed, B, cin, cout, P, kp], cuda_dev)
+    val = torch.empty(B, cout, device=cuda_dev)
+    arg = torch.empty(B, cout, dtype=torch.int32, device=cuda_dev)
+    _cabi.call("apb_pmax_decode", [packed, val, arg, B * cout], cuda_dev)
+    want_v = y.max(dim=2)[0]
+    first = (y == want_v[:, :, None]).float().argmax(dim=2)
+    assert torch.equal(val, want_v)
+    assert torch.equal(arg.long(), first)
+
+
+def test_conv_bn_block_fused_stats_matches_unfused(cuda_dev):
+    """ConvBlock (Conv -> BatchNorm -> ReLU) with the statistics taken in the GEMM epilogue vs the separate statistics
+    pass (apb_bn_stats_f32) over the same conv output: forward, gradients and running statistics."""
+    import copy
+    from adaptpoint_b200 import layers, norm, tcconv
+    torch.manual_seed(0)
+    blk = layers.create_convblock2d(35, 64, norm_args={"norm": "bn"}, act_args={"act": "relu"}).to(cuda_dev).train()
+    ref = copy.deepcopy(blk)
+    x = torch.randn(4, 35, 256, 32, device=cuda_dev)
+    gy = torch.randn(4, 64, 256, 32, device=cuda_dev)
+    xa, xb = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+    with tcconv.conv_backend("tc"):
+        ya = blk(xa)                                              # fused statistics
+        ya.backward(gy)
+        yb = ref[1].forward_act(ref[0](xb), True)                 # conv, then BatchNorm with its own statistics pass
+        yb.backward(gy)
+    assert _rel(ya, yb) < 1e-4
+    assert _rel(xa.grad, xb.grad) < 1e-4
+    assert _rel(blk[0].weight.grad, ref[0].weight.grad) < 1e-4
+    assert _rel(blk[1].weight.grad, ref[1].weight.grad) < 1e-4
+    assert _rel(blk[1].running_var, ref[1].running_var) < 1e-4 and _rel(blk[1].running_mean, ref[1].running_mean) < 1e-4

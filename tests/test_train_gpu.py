@@ -109,7 +109,7 @@ def test_fused_eval_after_replays_is_not_stale(cuda_dev):
     tr.classifier.eval()
     with torch.no_grad(), tcconv.conv_backend("tc"):
         tr.classifier(data)                                  # populate the cache in eager mode
-    tr.set_lr(c=0.05)                                        # make the classifier move visibly
+    tr.set_lr(c=0.01)                                        # make the classifier move visibly
     for _ in range(3):
         tr.step(pts.clone(), y)
     torch.cuda.synchronize()
