@@ -392,6 +392,89 @@ int launch_cm(CmParams p, const float *x, const float *w, int Kp, cudaStream_t s
     return APB_OK;
 }
 
+
+// ---- tiny layers in exact fp32 on the CUDA cores ------------------------------------------------------------------------
+// Layers with <= 16 output channels or <= 8 input channels (the imitator's mask / probability heads: 64 -> 3, 6 -> 2,
+// 1024 -> 3; the xyz embeddings 3 -> 64) hold no FLOPs worth a tensor core -- they are pure streaming -- but their
+// outputs feed a tau = 0.1 Gumbel soft-max and tanh / sigmoid heads, where TF32 operand rounding is amplified 10x.  cuDNN
+// makes the same call for such shapes (no TF32 kernel is selected), so computing them in fp32 keeps the product path as
+// close to the reference's default precision as the large layers are.  One thread per point, lanes = consecutive points.
+constexpr int TINY_COUT = 16, TINY_CIN = 8;
+
+__global__ void __launch_bounds__(256) pwconv_small_cout_kernel(const float *__restrict__ x, const float *__restrict__ w,
+                                                                const float *__restrict__ scale,
+                                                                const float *__restrict__ shift, int relu,
+                                                                float *__restrict__ y, int Cin, int Cout, int P, int Kp) {
+    extern __shared__ float sw[];   // [Cout][Cin]
+    const int b = blockIdx.y;
+    for (int i = threadIdx.x; i < Cout * Cin; i += 256) sw[i] = w[(size_t)(i / Cin) * Kp + (i % Cin)];
+    __syncthreads();
+    const int pp = blockIdx.x * 256 + threadIdx.x;
+    if (pp >= P) return;
+    const float *xb = x + (size_t)b * Cin * P + pp;
+    float acc[TINY_COUT];
+#pragma unroll
+    for (int c = 0; c < TINY_COUT; ++c) acc[c] = 0.f;
+    for (int k = 0; k < Cin; ++k) {
+        const float v = __ldg(xb + (size_t)k * P);
+#pragma unroll
+        for (int c = 0; c < TINY_COUT; ++c)
+            if (c < Cout) acc[c] = fmaf(sw[c * Cin + k], v, acc[c]);
+    }
+    float *yb = y + (size_t)b * Cout * P + pp;
+#pragma unroll
+    for (int c = 0; c < TINY_COUT; ++c) {
+        if (c < Cout) {
+            float v = acc[c];
+            if (scale) v *= scale[c];
+            if (shift) v += shift[c];
+            yb[(size_t)c * P] = relu ? fmaxf(v, 0.f) : v;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) pwconv_small_cin_kernel(const float *__restrict__ x, const float *__restrict__ w,
+                                                               const float *__restrict__ scale,
+                                                               const float *__restrict__ shift, int relu,
+                                                               float *__restrict__ y, int Cin, int Cout, int P, int Kp) {
+    extern __shared__ float sw[];   // [Cout][Cin]
+    const int b = blockIdx.y;
+    for (int i = threadIdx.x; i < Cout * Cin; i += 256) sw[i] = w[(size_t)(i / Cin) * Kp + (i % Cin)];
+    __syncthreads();
+    const int pp = blockIdx.x * 256 + threadIdx.x;
+    if (pp >= P) return;
+    const float *xb = x + (size_t)b * Cin * P + pp;
+    float v[TINY_CIN];
+#pragma unroll
+    for (int k = 0; k < TINY_CIN; ++k) v[k] = k < Cin ? __ldg(xb + (size_t)k * P) : 0.f;
+    float *yb = y + (size_t)b * Cout * P + pp;
+    for (int c = 0; c < Cout; ++c) {
+        float acc = 0.f;
+#pragma unroll
+        for (int k = 0; k < TINY_CIN; ++k)
+            if (k < Cin) acc = fmaf(sw[c * Cin + k], v[k], acc);
+        if (scale) acc *= scale[c];
+        if (shift) acc += shift[c];
+        yb[(size_t)c * P] = relu ? fmaxf(acc, 0.f) : acc;
+    }
+}
+
+int launch_tiny(const float *x, const float *w, const float *scale, const float *shift, int relu, float *y, int B, int Cin,
+                int Cout, int P, int Kp, cudaStream_t st) {
+    if (B > 65535 || (size_t)Cin * Cout * 4 > 96 * 1024) return APB_E_UNSUPPORTED;
+    const size_t smem = (size_t)Cin * Cout * 4;
+    const dim3 grid(apb_div_up(P, 256), B);
+    if (Cout <= TINY_COUT) {
+        APB_CUDA(cudaFuncSetAttribute((const void *)pwconv_small_cout_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        pwconv_small_cout_kernel<<<grid, 256, smem, st>>>(x, w, scale, shift, relu, y, Cin, Cout, P, Kp);
+    } else {
+        APB_CUDA(cudaFuncSetAttribute((const void *)pwconv_small_cin_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        pwconv_small_cin_kernel<<<grid, 256, smem, st>>>(x, w, scale, shift, relu, y, Cin, Cout, P, Kp);
+    }
+    APB_CHECK_LAUNCH();
+    return APB_OK;
+}
+
 bool cm_supported(const void *x, const void *w, int P, int Kp) {
     return (P % 4) == 0 && (Kp % CM_KC) == 0 && ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w)) & 15) == 0;
 }
@@ -407,6 +490,8 @@ extern "C" int apb_pwconv_fwd_tf32(const float *x, const float *w, const float *
     if (B < 0 || Cin <= 0 || Cout <= 0 || P < 0 || Kp < Cin) return APB_E_INVALID;
     if (B == 0 || P == 0) return APB_OK;
     if (!x || !w || !y) return APB_E_INVALID;
+    if ((Cout <= TINY_COUT || Cin <= TINY_CIN) && (size_t)Cin * Cout * 4 <= 96 * 1024 && B <= 65535)
+        return launch_tiny(x, w, scale, shift, relu, y, B, Cin, Cout, P, Kp, (cudaStream_t)stream);
     if (!cm_supported(x, w, P, Kp)) {
         if (Cout > 512 || (scale == nullptr) != (shift == nullptr)) return APB_E_UNSUPPORTED;
         return apb_pwconv_fwd_tf32_rows(x, w, scale, shift, relu, y, B, Cin, Cout, P, Kp, stream);

@@ -48,10 +48,17 @@ def _fusable(grouper, convs, feature_type, reduction, training):
 
 
 def _aggregate(mod, query_p, p, f):
-    """grouper -> concat -> convs -> pool; one fused call (tcgen05 shared MLP, no (B,C,M,K) tensors) when allowed."""
+    """grouper -> concat -> convs -> pool without the (B,C,M,K) tensors when a fused path covers the block:
+      * eval mode, no autograd, `fused=True`: bf16 tcgen05 shared MLP (fused.py, csrc/sa_fused.cu);
+      * one-conv blocks under autograd, training or eval mode (every block of PointNeXt-B/L/XL): fused_train.py,
+        csrc/sa_train.cu -- forward and backward;
+    otherwise the reference's op sequence over the same C-ABI kernels."""
     if mod.fused and _fusable(mod.grouper, mod.convs, mod.feature_type, mod.reduction, mod.training):
         from . import fused
         return fused.sa_fused_forward(mod, mod.grouper, mod.convs, query_p, p, f)
+    from . import fused_train
+    if fused_train.usable(mod, mod.grouper, mod.convs, mod.feature_type, mod.reduction, query_p, p, f):
+        return fused_train.sa_one_layer(mod, mod.grouper, mod.convs, query_p, p, f)
     dp, fj = mod.grouper(query_p, p, f)
     return _convs_pool(mod, get_aggregation_feautres(query_p, dp, None, fj, "dp_fj"))
 

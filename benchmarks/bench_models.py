@@ -5,11 +5,15 @@
   (N>1: python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 ... benchmarks/bench_models.py --gpus N)
 
 One step = forward + loss + backward + flat NCCL gradient all-reduce (train.allreduce_grads) + AdamW update of one
-per-GPU batch held in HBM, launched eagerly (no CUDA graph: this is the plain model path a user of
-`build_model(...)` gets).  `--graph` captures that step once (side-stream warm-up, capturable fused AdamW, the NCCL
-all-reduce inside the capture: the pattern of train.AdaptPointTrainer.capture_graph) and replays it; written after
-round 1's GPU budget was spent, so it has no committed measurement yet (gap 6).  Timing: CUDA events around the K timed steps, barrier + synchronize on both sides,
-max over ranks; samples/s is the whole job (weak scaling, per-GPU batch fixed).  One JSON line per case on rank 0.
+per-GPU batch held in HBM.  By default the step is captured once as ONE CUDA graph (side-stream warm-up, capturable
+fused AdamW, the NCCL all-reduce inside the capture: the pattern of train.AdaptPointTrainer.capture_graph) and
+replayed; `--eager` launches it kernel by kernel (the plain `build_model(...)` path, host-launch bound: round 1's
+0.85 / 0.63 at N=8).  Per-GPU batches are SURVEY.md 8d's: 32 clouds of 8192 points (B, L), 8 clouds of 24000 points
+(XL); `--batch` overrides.  The gradient all-reduce is one flat collective after the backward pass: 15-166 MB over
+NVLink is 0.1-0.5 ms of a 30-120 ms step, so bucketing it under the backward pass would buy < 0.5 %.
+Timing: CUDA events around the K timed steps, barrier + synchronize on both sides, max over ranks; samples/s is the
+whole job (weak scaling, per-GPU batch fixed); SM clocks / throttle reasons sampled (nvidia-smi, 100 ms) during the
+timed region of every case.  One JSON line per case on rank 0.
 Inputs are synthetic (seeded unit-ball clouds, xyz + height), weights random-init.  bench.py stays the driver's
 contract (configs[1]); this file only records configs[3]/[4] beside it.
 """
@@ -27,9 +31,9 @@ import torch.distributed as dist  # noqa: E402
 
 # name -> (CONFIGS key, per-GPU batch, points, classes); shapes of BASELINE.json configs[3] / configs[4]
 CASES = {
-    "b-cls": ("pointnext-b-cls", 8, 8192, 40),
-    "l-cls": ("pointnext-l-cls", 8, 8192, 40),
-    "xl-seg": ("pointnext-xl-seg", 2, 24000, 13),
+    "b-cls": ("pointnext-b-cls", 32, 8192, 40),
+    "l-cls": ("pointnext-l-cls", 32, 8192, 40),
+    "xl-seg": ("pointnext-xl-seg", 8, 24000, 13),
 }
 
 
@@ -48,6 +52,8 @@ def run_case(name, args, rank, world, dev):
     from adaptpoint_b200.models import build_model
     from adaptpoint_b200.train import allreduce_grads
     key, B, N, classes = CASES[name]
+    if args.batch:
+        B = args.batch
     seg = key.endswith("seg")
     torch.manual_seed(0)                       # same initial weights on every rank
     model = build_model(key).to(dev).train()
@@ -90,15 +96,20 @@ def run_case(name, args, rank, world, dev):
             graph.replay()
             return g_loss
 
-    for _ in range(args.warmup):
+    from bench import ClockSampler
+    for _ in range(max(args.warmup, 3)):
         loss = step()
     barrier()
+    sampler = ClockSampler(dev.index)
+    if rank == 0:
+        sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
         loss = step()
     e1.record()
     barrier()
+    clocks = sampler.stop() if rank == 0 else None
     ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
@@ -107,7 +118,7 @@ def run_case(name, args, rank, world, dev):
     if rank == 0:
         print(json.dumps({
             "metric": f"pointnext_{name.replace('-', '_')}_train_samples_per_s", "value": round(B * world / ms_step * 1e3, 2),
-            "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "clocks": clocks,
             "ms_per_step": round(ms_step, 3), "higher_is_better": True, "scaling": "weak",
             "dtype": "tf32" if args.conv == "tc" else "f32",
             "data": "synthetic", "loss": round(float(loss.detach()), 4), "hbm_peak_alloc_gib": round(peak_gb, 2),
@@ -116,7 +127,10 @@ def run_case(name, args, rank, world, dev):
                                    f"{'one CUDA graph' if args.graph else 'eager'}, "
                                    f"1x1 convs: {'libapb200 tcgen05 tf32' if args.conv == 'tc' else 'cuDNN fp32'}",
                        "parallelism": f"dp{world}"}}), flush=True)
-    graph = None                               # a graph holding NCCL work must go before destroy_process_group
+    if graph is not None:                      # a graph holding NCCL work must go before destroy_process_group
+        torch.cuda.synchronize()
+        graph.reset()
+        graph = None
     del model, opt
     torch.cuda.empty_cache()
     torch.cuda.reset_peak_memory_stats()
@@ -125,11 +139,15 @@ def run_case(name, args, rank, world, dev):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--cases", default="b-cls,xl-seg")
+    ap.add_argument("--cases", default="b-cls,l-cls,xl-seg")
     ap.add_argument("--conv", default="tc", choices=["tc", "torch"])
-    ap.add_argument("--graph", action="store_true", help="capture the step in one CUDA graph and replay it")
+    ap.add_argument("--eager", dest="graph", action="store_false", help="launch the step kernel by kernel instead of "
+                    "replaying one CUDA graph")
+    ap.add_argument("--graph", dest="graph", action="store_true", help="(default) capture the step in one CUDA graph")
+    ap.add_argument("--batch", type=int, default=0, help="per-GPU batch override (default: SURVEY 8d's 32 / 32 / 8)")
+    ap.set_defaults(graph=True)
     args = ap.parse_args()
     if not torch.cuda.is_available():
         raise SystemExit("bench_models.py needs a CUDA device (no CPU fallback)")

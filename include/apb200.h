@@ -212,6 +212,30 @@ int apb_rowmax_f32(const float *y, float *vmax, int32_t *arg, long long rows, in
 int apb_bnmax_bwd_f32(const float *y, const float *gsel, const int32_t *arg, const float *a, const float *bcoef,
                       float *dy, int B, int C, int M, int K, apb_stream_t stream);
 
+/* Training-mode set abstraction for one-conv blocks without the (B,C,M,K) tensors, forward and backward
+ * (csrc/sa_train.cu; replaces the chain QueryAndGroup -> cat -> Conv2d -> BatchNorm2d -> ReLU -> max over K of
+ * openpoints/models/backbone/pointnext.py:66-77, :164-166 for LocalAggregation and sa_layers = 1 SetAbstraction).
+ * u_pm (B,N,C) = Wf . f per support point, point-major (apb_pwconv_ex_tf32 with point_major = 1); wp (C,3) = xyz part of
+ * the conv weight (already divided by the radius when normalize_dp);  y[b,m,k,c] = u_pm[b,idx,c] + wp[c,:].(p[idx]-q[m]).
+ *   apb_group_ystats_f32 : vmax/vmin (B,C,M) = max/min over k of y, arg (B,C,M) = kmax | kmin << 16, stats (C,2) f64 +=
+ *                          sum y, sum y^2 (NULL: skip).  C % 4 == 0.
+ *   apb_sa1_bwd_count_f32: cnt (B,N) f32 += occurrences of n in idx[b]; sdp (B,N,3) += sum of (p[n]-q[m]) over them;
+ *                          mom (12) f64 += [sum dp (3), sum dp dp^T (9)].  All pre-zeroed by the caller.
+ *   apb_sa1_bwd_sparse_f32: for every (b,c,m): du_cm[b,c,idx[b,m,ksel]] += gs; dwp[c,:] += gs*dp (f64, NULL: skip);
+ *                          dxyz[b,n,:] += gs*wp[c,:], dq[b,m,:] -= gs*wp[c,:] (NULL: no coordinate gradient).
+ *   apb_sa1_bwd_dense_f32: du_cm[b,c,n] += cnt*a[c] + bc[c]*(cnt*u_pm[b,n,c] + wp[c,:].sdp[b,n]);
+ *                          usdp (C,3) f64 += sum_n u_pm[b,n,c]*sdp[b,n,:]   (the dense BatchNorm-backward terms). */
+int apb_group_ystats_f32(const float *u_pm, const float *xyz, const float *new_xyz, const int32_t *idx, const float *wp,
+                         float *vmax, float *vmin, int32_t *arg, double *stats, int B, int N, int M, int K, int C,
+                         apb_stream_t stream);
+int apb_sa1_bwd_count_f32(const float *xyz, const float *new_xyz, const int32_t *idx, float *cnt, float *sdp, double *mom,
+                          int B, int N, int M, int K, apb_stream_t stream);
+int apb_sa1_bwd_sparse_f32(const float *gs, const int32_t *ksel, const int32_t *idx, const float *xyz,
+                           const float *new_xyz, const float *wp, float *du_cm, double *dwp, float *dxyz, float *dq, int B,
+                           int N, int M, int K, int C, apb_stream_t stream);
+int apb_sa1_bwd_dense_f32(const float *u_pm, const float *cnt, const float *sdp, const float *a, const float *bc,
+                          const float *wp, float *du_cm, double *usdp, int B, int N, int C, apb_stream_t stream);
+
 /* Multi-head self-attention of the imitator (generator_component4_15.py:434-480, Anchor_selfattention.forward:
  * attn = softmax(q k^T / sqrt(d)); out = attn v), head_dim = 16 only (APB_E_UNSUPPORTED otherwise), fp32, scores never
  * materialised.  q,k,v,o,dout,dq,dk,dv: (B, M, H*16) token-major, 16-byte aligned; lse, delta: (B,H,M) f32 (lse =

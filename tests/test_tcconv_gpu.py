@@ -168,7 +168,7 @@ def test_tma_gemm_store_stats_pointmajor(cuda_dev, B, cin, cout, P):
     assert _rel(ypm, want_pm) < 3e-3
 
 
-@pytest.mark.parametrize("B,cin,cout,P", [(32, 128, 1024, 2048), (3, 64, 96, 1000), (2, 3, 64, 100), (4, 128, 300, 388)])
+@pytest.mark.parametrize("B,cin,cout,P", [(32, 128, 1024, 2048), (3, 64, 96, 1000), (2, 12, 64, 100), (4, 128, 300, 388)])
 def test_tma_gemm_max_over_points_exact(cuda_dev, B, cin, cout, P):
     """The max / first-arg-max epilogue must agree EXACTLY with a max over the activation the store epilogue of the same
     kernel writes (same MMA order => same bits)."""
