@@ -435,6 +435,104 @@ __global__ void __launch_bounds__(NT) affine_small_kernel(const float *__restric
 
 bool grid_ok(int B, int C) { return B <= 65535 && C <= 65535; }
 
+
+// ---- the small-tensor arithmetic around BatchNorm -> max over K (norm.BNMaxFn, fused_train.SaOneLayerFn) ---------------
+// From the (C,2) sums to (mean, rstd, scale, shift), the running-statistics update, the max/min selection by the sign of
+// the scale, the affine map and the ReLU: ONE kernel instead of ~28 element-wise torch launches per block and pass.
+struct BnMaxFinParams {
+    const double *stats;   // (C,2) sum, sum of squares over all ranks; nullptr: eval mode (running statistics)
+    double inv_count, unbias;
+    float eps, momentum;
+    const float *gamma, *beta;
+    float *running_mean, *running_var;   // read in eval mode, updated in training mode (may be nullptr there)
+    const float *vmax, *vmin;
+    const int32_t *arg;                  // kmax | kmin << 16
+    int relu;
+    float *out, *sel;
+    int32_t *ksel;
+    float *scale, *mean, *rstd;          // (C) saved for the backward pass
+    int C, M;
+};
+
+__global__ void __launch_bounds__(NT) bnmax_finalize_kernel(const BnMaxFinParams p) {
+    const int c = blockIdx.y, b = blockIdx.z;
+    float mean, rstd;
+    if (p.stats != nullptr) {
+        const double mean_d = p.stats[2 * c] * p.inv_count;
+        double var_d = p.stats[2 * c + 1] * p.inv_count - mean_d * mean_d;
+        if (var_d < 0.0) var_d = 0.0;
+        mean = (float)mean_d;
+        rstd = (float)(1.0 / sqrt(var_d + (double)p.eps));
+        if (b == 0 && blockIdx.x == 0 && threadIdx.x == 0 && p.running_mean != nullptr) {
+            p.running_mean[c] = (1.f - p.momentum) * p.running_mean[c] + p.momentum * mean;
+            p.running_var[c] = (1.f - p.momentum) * p.running_var[c] + p.momentum * (float)(var_d * p.unbias);
+        }
+    } else {
+        mean = p.running_mean[c];
+        rstd = rsqrtf(p.running_var[c] + p.eps);
+    }
+    const float scale = p.gamma[c] * rstd;
+    const float shift = p.beta[c] - mean * scale;
+    if (b == 0 && blockIdx.x == 0 && threadIdx.x == 0) {
+        p.scale[c] = scale;
+        p.mean[c] = mean;
+        p.rstd[c] = rstd;
+    }
+    const bool pos = scale >= 0.f;
+    const size_t base = ((size_t)b * p.C + c) * p.M;
+    for (int m = blockIdx.x * NT + threadIdx.x; m < p.M; m += gridDim.x * NT) {
+        const float v = pos ? p.vmax[base + m] : p.vmin[base + m];
+        const int a = p.arg[base + m];
+        float o = fmaf(v, scale, shift);
+        if (p.relu) o = fmaxf(o, 0.f);
+        p.out[base + m] = o;
+        p.sel[base + m] = v;
+        p.ksel[base + m] = pos ? (a & 0xFFFF) : (a >> 16);
+    }
+}
+
+// gs = g * [out > 0] * scale ; sums (C,2) f64 += [sum g*mask, sum g*mask*xhat(sel)]
+__global__ void __launch_bounds__(NT) bnmax_bwd_reduce_kernel(const float *__restrict__ g, const float *__restrict__ out,
+                                                              const float *__restrict__ sel,
+                                                              const float *__restrict__ scale,
+                                                              const float *__restrict__ mean,
+                                                              const float *__restrict__ rstd, float *__restrict__ gs,
+                                                              double *__restrict__ sums, int C, int M) {
+    const int c = blockIdx.y, b = blockIdx.z;
+    const float sc = scale[c], mu = mean[c], rs = rstd[c];
+    const size_t base = ((size_t)b * C + c) * M;
+    float s = 0.f, q = 0.f;
+    for (int m = blockIdx.x * NT + threadIdx.x; m < M; m += gridDim.x * NT) {
+        float gv = g[base + m];
+        if (out != nullptr && !(out[base + m] > 0.f)) gv = 0.f;
+        gs[base + m] = gv * sc;
+        s += gv;
+        q = fmaf(gv, (sel[base + m] - mu) * rs, q);
+    }
+    block_sum2(s, q);
+    if (threadIdx.x == 0) {
+        atomicAdd(sums + 2 * c, (double)s);
+        atomicAdd(sums + 2 * c + 1, (double)q);
+    }
+}
+
+// per channel: BatchNorm-backward coefficients of the dense terms (training) and the parameter gradients
+__global__ void bnmax_bwd_coef_kernel(const double *__restrict__ tot, const double *__restrict__ local,
+                                      const float *__restrict__ scale, const float *__restrict__ mean,
+                                      const float *__restrict__ rstd, double inv_count, float *__restrict__ a,
+                                      float *__restrict__ bcoef, float *__restrict__ dgamma, float *__restrict__ dbeta,
+                                      int C) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    dbeta[c] = (float)local[2 * c];
+    dgamma[c] = (float)local[2 * c + 1];
+    if (a != nullptr) {
+        const float bc = (float)(-(double)scale[c] * (double)rstd[c] * tot[2 * c + 1] * inv_count);
+        bcoef[c] = bc;
+        a[c] = (float)(-(double)scale[c] * tot[2 * c] * inv_count) - bc * mean[c];
+    }
+}
+
 }  // namespace
 
 // vmax[r] = max_p y[r,p], arg[r] = first p attaining it.   One warp per row, 16-byte loads.
@@ -601,6 +699,59 @@ extern "C" int apb_rowmax_f32(const float *y, float *vmax, int32_t *arg, long lo
     if (!y || !vmax || !arg || P == 0) return APB_E_INVALID;
     if (rows > 8LL * 2147483647LL) return APB_E_UNSUPPORTED;
     rowmax_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, (cudaStream_t)stream>>>(y, vmax, arg, rows, P);
+    APB_CHECK_LAUNCH();
+    return APB_OK;
+}
+
+extern "C" int apb_bnmax_finalize_f32(const double *stats, double count, float eps, float momentum, const float *gamma,
+                                      const float *beta, float *running_mean, float *running_var, const float *vmax,
+                                      const float *vmin, const int32_t *arg, int relu, float *out, float *sel,
+                                      int32_t *ksel, float *scale, float *mean, float *rstd, int B, int C, int M,
+                                      apb_stream_t stream) {
+    if (B < 0 || C <= 0 || M < 0) return APB_E_INVALID;
+    if (B == 0 || M == 0) return APB_OK;
+    if (!gamma || !beta || !vmax || !vmin || !arg || !out || !sel || !ksel || !scale || !mean || !rstd) return APB_E_INVALID;
+    if (stats == nullptr && (!running_mean || !running_var)) return APB_E_INVALID;
+    if (B > 65535 || C > 65535) return APB_E_UNSUPPORTED;
+    BnMaxFinParams p{};
+    p.stats = stats;
+    p.inv_count = count > 0 ? 1.0 / count : 0.0;
+    p.unbias = count > 1 ? count / (count - 1.0) : 1.0;
+    p.eps = eps; p.momentum = momentum; p.gamma = gamma; p.beta = beta;
+    p.running_mean = running_mean; p.running_var = running_var;
+    p.vmax = vmax; p.vmin = vmin; p.arg = arg; p.relu = relu; p.out = out; p.sel = sel; p.ksel = ksel;
+    p.scale = scale; p.mean = mean; p.rstd = rstd; p.C = C; p.M = M;
+    int gx = apb_div_up(M, NT);
+    if (gx > 8) gx = 8;
+    bnmax_finalize_kernel<<<dim3(gx, C, B), NT, 0, (cudaStream_t)stream>>>(p);
+    APB_CHECK_LAUNCH();
+    return APB_OK;
+}
+
+extern "C" int apb_bnmax_bwd_reduce_f32(const float *g, const float *out_relu, const float *sel, const float *scale,
+                                        const float *mean, const float *rstd, float *gs, double *sums, int B, int C, int M,
+                                        apb_stream_t stream) {
+    if (B < 0 || C <= 0 || M < 0) return APB_E_INVALID;
+    if (B == 0 || M == 0) return APB_OK;
+    if (!g || !sel || !scale || !mean || !rstd || !gs || !sums) return APB_E_INVALID;
+    if (B > 65535 || C > 65535) return APB_E_UNSUPPORTED;
+    int gx = apb_div_up(M, NT * 4);
+    if (gx > 8) gx = 8;
+    bnmax_bwd_reduce_kernel<<<dim3(gx, C, B), NT, 0, (cudaStream_t)stream>>>(g, out_relu, sel, scale, mean, rstd, gs, sums,
+                                                                             C, M);
+    APB_CHECK_LAUNCH();
+    return APB_OK;
+}
+
+extern "C" int apb_bnmax_bwd_coef_f32(const double *tot, const double *local, const float *scale, const float *mean,
+                                      const float *rstd, double count, float *a, float *bcoef, float *dgamma,
+                                      float *dbeta, int C, apb_stream_t stream) {
+    if (C <= 0) return APB_E_INVALID;
+    if (!tot || !local || !scale || !mean || !rstd || !dgamma || !dbeta || ((a == nullptr) != (bcoef == nullptr)))
+        return APB_E_INVALID;
+    bnmax_bwd_coef_kernel<<<apb_div_up(C, 128), 128, 0, (cudaStream_t)stream>>>(tot, local, scale, mean, rstd,
+                                                                                count > 0 ? 1.0 / count : 0.0, a, bcoef,
+                                                                                dgamma, dbeta, C);
     APB_CHECK_LAUNCH();
     return APB_OK;
 }

@@ -75,27 +75,11 @@ class SaOneLayerFn(Function):
         arg = torch.empty((B, C1, M), dtype=torch.int32, device=dev)
         stats = torch.zeros((C1, 2), dtype=torch.float64, device=dev) if training else None
         _cabi.call("apb_group_ystats_f32", [u, ps, qs, idx, wp, vmax, vmin, arg, stats, B, N, M, K, C1], dev)
+        n = 1.0
         if training:
-            world = norm._allreduce(stats, group)
-            n = float(B * M * K * world)
-            mean_d = stats[:, 0] / n
-            var_d = (stats[:, 1] / n - mean_d * mean_d).clamp_min(0.0)
-            mean, rstd = mean_d.float(), torch.rsqrt(var_d + eps).float()
-            if running_mean is not None:
-                with torch.no_grad():
-                    running_mean.mul_(1 - momentum).add_(mean, alpha=momentum)
-                    running_var.mul_(1 - momentum).add_((var_d * (n / max(n - 1.0, 1.0))).float(), alpha=momentum)
-        else:
-            n = 1.0
-            mean, rstd = running_mean.float(), torch.rsqrt(running_var.float() + eps)
-        scale = gamma * rstd
-        shift = beta - mean * scale
-        pos = (scale >= 0).view(1, C1, 1)
-        sel = torch.where(pos, vmax, vmin)
-        ksel = torch.where(pos, arg & 0xFFFF, arg >> 16)
-        out = sel * scale.view(1, C1, 1) + shift.view(1, C1, 1)
-        if relu:
-            out = out.clamp_min_(0.0)
+            n = float(B * M * K * norm._allreduce(stats, group))
+        out, sel, ksel, scale, mean, rstd = norm.bnmax_post(vmax, vmin, arg, stats, n, gamma, beta, running_mean,
+                                                            running_var, momentum, eps, relu, training)
         ctx.save_for_backward(ps, qs, fs, idx, u, sel, ksel, out if relu else None, scale, mean, rstd, wp, wf)
         ctx.cfg = (relu, training, group, n, inv_r, tuple(conv_w.shape))
         return out
@@ -108,27 +92,14 @@ class SaOneLayerFn(Function):
         M, K = idx.shape[1], idx.shape[2]
         C1, cin = wf.shape
         dev = fs.device
-        g = g.contiguous().float()
-        if relu:
-            g = g * (out > 0)
-        sg = g.sum(dim=(0, 2))
-        sgx = (g * ((sel - mean.view(1, C1, 1)) * rstd.view(1, C1, 1))).sum(dim=(0, 2))
-        gs = (g * scale.view(1, C1, 1)).contiguous()
+        gs, a, bcoef, sgx, sg = norm.bnmax_bwd_prep(g.contiguous().float(), out, sel, scale, mean, rstd, training, group, n)
         need_w = ctx.needs_input_grad[4]
         du = torch.zeros((B, C1, N), dtype=torch.float32, device=dev)
         dwp = torch.zeros((C1, 3), dtype=torch.float64, device=dev) if need_w else None
         dxyz = torch.zeros_like(ps) if ctx.needs_input_grad[0] else None
         dq = torch.zeros_like(qs) if ctx.needs_input_grad[1] else None
-        _cabi.call("apb_sa1_bwd_sparse_f32", [gs, ksel.contiguous(), idx, ps, qs, wp, du, dwp, dxyz, dq, B, N, M, K, C1],
-                   dev)
+        _cabi.call("apb_sa1_bwd_sparse_f32", [gs, ksel, idx, ps, qs, wp, du, dwp, dxyz, dq, B, N, M, K, C1], dev)
         if training:
-            tot = torch.stack([sg, sgx])
-            if group is not None:
-                tot = tot.clone()
-                norm._allreduce(tot, group)
-            tsg, tsgx = tot[0], tot[1]
-            bcoef = (-scale * rstd * tsgx / n).contiguous()
-            a = (-scale * tsg / n - bcoef * mean).contiguous()
             cnt = torch.zeros((B, N), dtype=torch.float32, device=dev)
             sdp = torch.zeros((B, N, 3), dtype=torch.float32, device=dev)
             mom = torch.zeros(12, dtype=torch.float64, device=dev)

@@ -122,6 +122,41 @@ class BatchNormEvalFn(Function):
         return dx, dgamma, dbeta, None, None, None, None
 
 
+def bnmax_post(vmax, vmin, arg, stats, n, weight, bias, running_mean, running_var, momentum, eps, relu, training):
+    """Everything between the per-(b,c,m) max/min and the block's output, in one kernel (apb_bnmax_finalize_f32):
+    statistics -> (mean, rstd, scale), running-statistics update, max-or-min by the sign of the scale, affine, ReLU.
+    -> out, sel, ksel (B,C,M), scale, mean, rstd (C)."""
+    B, C, M = vmax.shape
+    dev = vmax.device
+    out, sel = torch.empty_like(vmax), torch.empty_like(vmax)
+    ksel = torch.empty((B, C, M), dtype=torch.int32, device=dev)
+    scale, mean, rstd = (torch.empty(C, dtype=torch.float32, device=dev) for _ in range(3))
+    _cabi.call("apb_bnmax_finalize_f32", [stats if training else None, float(n), float(eps), float(momentum or 0.0),
+                                          weight.detach(), bias.detach(), running_mean, running_var, vmax, vmin, arg,
+                                          int(relu), out, sel, ksel, scale, mean, rstd, B, C, M], dev)
+    return out, sel, ksel, scale, mean, rstd
+
+
+def bnmax_bwd_prep(g, out_relu, sel, scale, mean, rstd, training, group, n):
+    """-> gs = g*[out>0]*scale (B,C,M); a, bcoef (C) of the dense BatchNorm-backward terms (None in eval mode); dgamma,
+    dbeta (C) per rank.  Two kernels (+ the SyncBN all-reduce of the two channel sums between them)."""
+    B, C, M = g.shape
+    dev = g.device
+    gs = torch.empty_like(g)
+    sums = torch.zeros((C, 2), dtype=torch.float64, device=dev)
+    _cabi.call("apb_bnmax_bwd_reduce_f32", [g, out_relu, sel, scale, mean, rstd, gs, sums, B, C, M], dev)
+    tot = sums
+    if training and group is not None and dist.is_initialized() and dist.get_world_size(group) > 1:
+        tot = sums.clone()
+        _allreduce(tot, group)
+    a = bcoef = None
+    if training:
+        a, bcoef = torch.empty(C, dtype=torch.float32, device=dev), torch.empty(C, dtype=torch.float32, device=dev)
+    dgamma, dbeta = torch.empty(C, dtype=torch.float32, device=dev), torch.empty(C, dtype=torch.float32, device=dev)
+    _cabi.call("apb_bnmax_bwd_coef_f32", [tot, sums, scale, mean, rstd, float(n), a, bcoef, dgamma, dbeta, C], dev)
+    return gs, a, bcoef, dgamma, dbeta
+
+
 class BNMaxFn(Function):
     """out (B,C,M) = max_k relu?(BN(y))  for y (B,C,M,K); `training` selects batch vs running statistics."""
 
@@ -135,58 +170,26 @@ class BNMaxFn(Function):
         arg = torch.empty((B, C, M), dtype=torch.int32, device=dev)
         stats = torch.zeros((C, 2), dtype=torch.float64, device=dev) if training else None
         _cabi.call("apb_kmax_stats_f32", [ys, vmax, vmin, arg, stats, B, C, M, K], dev)
+        n = 1.0
         if training:
-            world = _allreduce(stats, group)
-            n = float(B * M * K * world)
-            mean_d = stats[:, 0] / n
-            var_d = (stats[:, 1] / n - mean_d * mean_d).clamp_min(0.0)
-            mean, rstd = mean_d.float(), torch.rsqrt(var_d + eps).float()
-            if running_mean is not None:
-                with torch.no_grad():
-                    running_mean.mul_(1 - momentum).add_(mean, alpha=momentum)
-                    running_var.mul_(1 - momentum).add_((var_d * (n / max(n - 1.0, 1.0))).float(), alpha=momentum)
-        else:
-            n = 1.0
-            mean, rstd = running_mean.float(), torch.rsqrt(running_var.float() + eps)
-        scale = weight * rstd
-        shift = bias - mean * scale
-        pos = (scale >= 0).view(1, C, 1)
-        sel = torch.where(pos, vmax, vmin)
-        arg_sel = torch.where(pos, arg & 0xFFFF, arg >> 16)
-        out = sel * scale.view(1, C, 1) + shift.view(1, C, 1)
-        if relu:
-            out = out.clamp_min_(0.0)
-        ctx.save_for_backward(ys, sel, arg_sel, out if relu else None, scale, mean, rstd)
+            n = float(B * M * K * _allreduce(stats, group))
+        out, sel, ksel, scale, mean, rstd = bnmax_post(vmax, vmin, arg, stats, n, weight, bias, running_mean,
+                                                       running_var, momentum, eps, relu, training)
+        ctx.save_for_backward(ys, sel, ksel, out if relu else None, scale, mean, rstd)
         ctx.cfg = (relu, training, group, n)
         return out
 
     @staticmethod
     def backward(ctx, g):
-        ys, sel, arg_sel, out, scale, mean, rstd = ctx.saved_tensors
+        ys, sel, ksel, out, scale, mean, rstd = ctx.saved_tensors
         relu, training, group, n = ctx.cfg
         B, C, M, K = ys.shape
         dev = ys.device
-        g = g.contiguous().float()
-        if relu:
-            g = g * (out > 0)
-        sg = g.sum(dim=(0, 2))
-        sgx = (g * ((sel - mean.view(1, C, 1)) * rstd.view(1, C, 1))).sum(dim=(0, 2))
-        dgamma, dbeta = sgx, sg
+        gs, a, bcoef, dgamma, dbeta = bnmax_bwd_prep(g.contiguous().float(), out, sel, scale, mean, rstd, training, group, n)
         dy = None
         if ctx.needs_input_grad[0]:
-            gsel = (g * scale.view(1, C, 1)).contiguous()
-            a = bcoef = None
-            if training:
-                tot = torch.stack([sg, sgx])
-                if group is not None:
-                    tot = tot.clone()
-                    _allreduce(tot, group)
-                tsg, tsgx = tot[0], tot[1]
-                bcoef = (-scale * rstd * tsgx / n).contiguous()
-                a = (-scale * tsg / n - bcoef * mean).contiguous()
             dy = torch.empty_like(ys)
-            _cabi.call("apb_bnmax_bwd_f32", [ys if training else None, gsel, arg_sel.contiguous(), a, bcoef, dy,
-                                             B, C, M, K], dev)
+            _cabi.call("apb_bnmax_bwd_f32", [ys if training else None, gs, ksel, a, bcoef, dy, B, C, M, K], dev)
         return dy, dgamma, dbeta, None, None, None, None, None, None, None
 
 

@@ -100,9 +100,16 @@ class PeerAllreduce:
             cur = torch.cuda.current_stream(self.device)
             capturing = self._serialise(cur)
             stream = ctypes.c_void_p(cur.cuda_stream)
+            trace = _cabi.TRACE
+            if trace is not None:          # bench.py's per-launch CUDA-event trace (eager steps only)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(cur)
             status = lib.apb_peer_allreduce(ctypes.c_void_p(t.data_ptr()), t.numel(),
                                             1 if t.dtype == torch.float64 else 0, self._ptrs, self.world, self.rank,
                                             stream)
+            if trace is not None:
+                e1.record(cur)
+                trace.append(("apb_peer_allreduce", (int(t.numel()), self.world), e0, e1))
             ev = torch.cuda.Event()
             ev.record(cur)
             self._last = (cur.cuda_stream, ev, capturing)

@@ -174,7 +174,8 @@ class PointwiseConvMaxFn(Function):
             wb, kp = pack_f32(w2d)
             packed = torch.zeros((B, cout), dtype=torch.int64, device=x.device)
             shift = None if bias is None else bias.detach().contiguous().float()
-            _cabi.call("apb_pwconv_ex_tf32", [xs, wb, None, shift, 0, None, 0, None, packed, B, cin, cout, P, kp],
+            # (point_major = 2 is ignored when `pmax` is given; it marks the call for bench.py's byte model)
+            _cabi.call("apb_pwconv_ex_tf32", [xs, wb, None, shift, 0, None, 2, None, packed, B, cin, cout, P, kp],
                        x.device)
             val = torch.empty((B, cout), dtype=torch.float32, device=x.device)
             arg32 = torch.empty((B, cout), dtype=torch.int32, device=x.device)

@@ -49,6 +49,11 @@ def allreduce_grads(params):
     grads = [p.grad for p in params if p.grad is not None]
     if not grads:
         return
+    from . import _cabi
+    trace = _cabi.TRACE if grads[0].is_cuda else None
+    if trace is not None:                  # bench.py's per-launch CUDA-event trace: flatten + collective + copy back
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
     flat = torch._utils._flatten_dense_tensors(grads)
     if dist.get_backend() == "nccl":
         dist.all_reduce(flat, op=dist.ReduceOp.AVG)      # the division rides in the collective
@@ -57,6 +62,9 @@ def allreduce_grads(params):
         flat.div_(world)
     # one multi-tensor copy instead of one small kernel per parameter
     torch._foreach_copy_(grads, list(torch._utils._unflatten_dense_tensors(flat, grads)))
+    if trace is not None:
+        e1.record()
+        trace.append(("nccl_allreduce_grads", (int(flat.numel()), world), e0, e1))
 
 
 def hard_ratio(epoch, cfg):

@@ -212,6 +212,25 @@ int apb_rowmax_f32(const float *y, float *vmax, int32_t *arg, long long rows, in
 int apb_bnmax_bwd_f32(const float *y, const float *gsel, const int32_t *arg, const float *a, const float *bcoef,
                       float *dy, int B, int C, int M, int K, apb_stream_t stream);
 
+/* The per-channel arithmetic around BatchNorm -> max over K, in three kernels instead of ~40 element-wise launches:
+ *   apb_bnmax_finalize_f32  : (stats (C,2) f64 over `count` elements | NULL = running statistics) -> mean, rstd,
+ *                             scale = gamma*rstd, running-statistics update (training), then per (b,c,m):
+ *                             sel = scale >= 0 ? vmax : vmin, ksel = its k (arg = kmax | kmin << 16),
+ *                             out = act(scale*sel + beta - mean*scale).
+ *   apb_bnmax_bwd_reduce_f32: gs = g * [out_relu > 0] * scale; sums (C,2) f64 += [sum g*mask, sum g*mask*(sel-mean)*rstd].
+ *   apb_bnmax_bwd_coef_f32  : dbeta, dgamma from the LOCAL sums; a, bcoef (dense BatchNorm-backward terms
+ *                             dy += a + bcoef*y) from the sums over all ranks (NULL, NULL in eval mode). */
+int apb_bnmax_finalize_f32(const double *stats, double count, float eps, float momentum, const float *gamma,
+                           const float *beta, float *running_mean, float *running_var, const float *vmax,
+                           const float *vmin, const int32_t *arg, int relu, float *out, float *sel, int32_t *ksel,
+                           float *scale, float *mean, float *rstd, int B, int C, int M, apb_stream_t stream);
+int apb_bnmax_bwd_reduce_f32(const float *g, const float *out_relu, const float *sel, const float *scale,
+                             const float *mean, const float *rstd, float *gs, double *sums, int B, int C, int M,
+                             apb_stream_t stream);
+int apb_bnmax_bwd_coef_f32(const double *tot, const double *local, const float *scale, const float *mean,
+                           const float *rstd, double count, float *a, float *bcoef, float *dgamma, float *dbeta, int C,
+                           apb_stream_t stream);
+
 /* Training-mode set abstraction for one-conv blocks without the (B,C,M,K) tensors, forward and backward
  * (csrc/sa_train.cu; replaces the chain QueryAndGroup -> cat -> Conv2d -> BatchNorm2d -> ReLU -> max over K of
  * openpoints/models/backbone/pointnext.py:66-77, :164-166 for LocalAggregation and sa_layers = 1 SetAbstraction).
