@@ -27,6 +27,7 @@ _SIGNATURES = {
     "apb_ball_query_f32": [_p, _p, _p, _i, _i, _i, _f, _i, _p],
     "apb_knn_f32": [_p, _p, _p, _p, _i, _i, _i, _i, _p],
     "apb_group_f32": [_p, _p, _p, _i, _i, _i, _i, _i, _p],
+    "apb_group_bf16": [_p, _p, _p, _i, _i, _i, _i, _i, _p],
     "apb_group_minmax_f32": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p],
     "apb_group_grad_f32": [_p, _p, _p, _i, _i, _i, _i, _i, _p],
     "apb_three_nn_f32": [_p, _p, _p, _p, _i, _i, _i, _p],

@@ -436,7 +436,15 @@ __global__ void __launch_bounds__(256) attn_small_bwd_kernel(const float *__rest
 
 bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
+constexpr int MMA_MIN_TOKENS = 33;   // attention_mma.cu (3xTF32 warp-level MMA) takes every call with more tokens
+
 }  // namespace
+
+// attention_mma.cu
+int apb_attn_mma_fwd(const float *q, const float *k, const float *v, float *o, float *lse, int B, int M, int H,
+                     cudaStream_t st);
+int apb_attn_mma_bwd(const float *q, const float *k, const float *v, const float *o, const float *dout, const float *lse,
+                     float *dq, float *dk, float *dv, float *delta, int B, int M, int H, cudaStream_t st);
 
 extern "C" int apb_attn_fwd_f32(const float *q, const float *k, const float *v, float *o, float *lse, int B, int M,
                                 int H, int head_dim, apb_stream_t stream) {
@@ -445,6 +453,7 @@ extern "C" int apb_attn_fwd_f32(const float *q, const float *k, const float *v, 
     if (!q || !k || !v || !o || !lse) return APB_E_INVALID;
     if (head_dim != D || B > 65535 || H > 65535) return APB_E_UNSUPPORTED;
     if (!aligned16(q) || !aligned16(k) || !aligned16(v) || !aligned16(o)) return APB_E_INVALID;
+    if (M >= MMA_MIN_TOKENS) return apb_attn_mma_fwd(q, k, v, o, lse, B, M, H, (cudaStream_t)stream);
     const float scale2 = 1.4426950408889634f / sqrtf((float)D);
     if (M > QT) {  // two queries per thread
         dim3 grid(apb_div_up(M, 2 * QT), H, B);
@@ -467,6 +476,8 @@ extern "C" int apb_attn_bwd_f32(const float *q, const float *k, const float *v, 
     if (!aligned16(q) || !aligned16(k) || !aligned16(v) || !aligned16(o) || !aligned16(dout) || !aligned16(dq) ||
         !aligned16(dk) || !aligned16(dv))
         return APB_E_INVALID;
+    if (M >= MMA_MIN_TOKENS)
+        return apb_attn_mma_bwd(q, k, v, o, dout, lse, dq, dk, dv, delta, B, M, H, (cudaStream_t)stream);
     const float scale = 1.f / sqrtf((float)D);
     const float scale2 = 1.4426950408889634f * scale;
     cudaStream_t st = (cudaStream_t)stream;

@@ -726,16 +726,25 @@ extern "C" int apb_three_interp_f32(const float *points, const int32_t *idx, con
     cudaStream_t st = (cudaStream_t)stream;
     const size_t row = (size_t)m * sizeof(float);
     const int xblocks = min(apb_div_up(n, GT), 4 * APB_NUM_SMS);
+    // A CTA stages CH rows of m floats and must produce enough output to pay for them: at least 4 output points per
+    // staged point (round 2's sweep: 8*GT points per CTA re-staged 128 KB for 32 KB of output at m = 8192 and ran
+    // BELOW the reference kernel), fewer only when the grid would otherwise not cover the SMs.
+    auto xgrid = [&](int groups) {
+        long long per = (long long)4 * m;
+        if (per < 8 * GT) per = 8 * GT;
+        while (per > 8 * GT && (long long)apb_div_up(n, per) * groups * B < 2 * APB_NUM_SMS) per >>= 1;
+        return (int)min((long long)xblocks, max(1LL, (long long)apb_div_up(n, per)));
+    };
     if (row * 4 <= kSmemBudget && C >= 4) {
         const size_t smem = row * 4;
         APB_CUDA(cudaFuncSetAttribute((const void *)three_interp_kernel<4>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        dim3 grid(min(xblocks, max(1, apb_div_up(n, 8 * GT))), apb_div_up(C, 4), B);
+        dim3 grid(xgrid(apb_div_up(C, 4)), apb_div_up(C, 4), B);
         three_interp_kernel<4><<<grid, GT, smem, st>>>(points, idx, weight, out, C, m, n);
     } else if (row <= kSmemBudget) {
         APB_CUDA(cudaFuncSetAttribute((const void *)three_interp_kernel<1>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)row));
-        dim3 grid(min(xblocks, max(1, apb_div_up(n, 8 * GT))), C, B);
+        dim3 grid(xgrid(C), C, B);
         three_interp_kernel<1><<<grid, GT, row, st>>>(points, idx, weight, out, C, m, n);
     } else {
         dim3 grid(xblocks, C, B);

@@ -394,8 +394,8 @@ int launch_cm(CmParams p, const float *x, const float *w, int Kp, cudaStream_t s
 
 
 // ---- tiny layers in exact fp32 on the CUDA cores ------------------------------------------------------------------------
-// Layers with <= 16 output channels or <= 8 input channels (the imitator's mask / probability heads: 64 -> 3, 6 -> 2,
-// 1024 -> 3; the xyz embeddings 3 -> 64) hold no FLOPs worth a tensor core -- they are pure streaming -- but their
+// Layers with <= 16 output channels or <= 8 input channels and at most 2048 weights, over >= 256 points (the imitator's
+// mask head 64 -> 3, 6 -> 2 and the xyz embeddings 3 -> 64 on 2048-point clouds) hold no FLOPs worth a tensor core -- they are pure streaming -- but their
 // outputs feed a tau = 0.1 Gumbel soft-max and tanh / sigmoid heads, where TF32 operand rounding is amplified 10x.  cuDNN
 // makes the same call for such shapes (no TF32 kernel is selected), so computing them in fp32 keeps the product path as
 // close to the reference's default precision as the large layers are.  One thread per point, lanes = consecutive points.
@@ -490,7 +490,8 @@ extern "C" int apb_pwconv_fwd_tf32(const float *x, const float *w, const float *
     if (B < 0 || Cin <= 0 || Cout <= 0 || P < 0 || Kp < Cin) return APB_E_INVALID;
     if (B == 0 || P == 0) return APB_OK;
     if (!x || !w || !y) return APB_E_INVALID;
-    if ((Cout <= TINY_COUT || Cin <= TINY_CIN) && (size_t)Cin * Cout * 4 <= 96 * 1024 && B <= 65535)
+    // (one thread per point: only worth it when there are points to spread over the SMs and the weight block is small)
+    if ((Cout <= TINY_COUT || Cin <= TINY_CIN) && Cin * Cout <= 2048 && P >= 256 && B <= 65535)
         return launch_tiny(x, w, scale, shift, relu, y, B, Cin, Cout, P, Kp, (cudaStream_t)stream);
     if (!cm_supported(x, w, P, Kp)) {
         if (Cout > 512 || (scale == nullptr) != (shift == nullptr)) return APB_E_UNSUPPORTED;

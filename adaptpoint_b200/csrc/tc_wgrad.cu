@@ -191,6 +191,10 @@ extern "C" int apb_pwconv_wgrad_tf32(const float *grad_y, const float *x, float 
     if (rc != APB_OK) return rc;
     APB_CUDA(cudaFuncSetAttribute((const void *)tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     long long ksplit = (long long)APB_NUM_SMS / (mtiles * ntiles);  // one wave: 1 CTA per SM (smem-bound)
+    // every split adds a full 128 x nb tile to gW with fp32 atomics: a CTA must have enough K to pay for that (a
+    // (256 -> 512, P = 64) layer split 37 ways spent 186 us in its 4.8 M atomics, round 2 trace)
+    const long long min_chunks = 16;
+    if (ksplit > p.total / min_chunks) ksplit = p.total / min_chunks;
     if (ksplit < 1) ksplit = 1;
     if (ksplit > p.total) ksplit = p.total;
     dim3 grid((unsigned)ksplit, mtiles, ntiles);

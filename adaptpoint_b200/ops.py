@@ -225,6 +225,18 @@ def self_attention(q, k, v, heads):
                          "kernel family (head_dim 16, or <= 32 tokens)")
 
 
+def grouping_operation_bf16(features, idx):
+    """grouping_operation for bf16 features (no autograd: the bf16 shared-MLP path is inference-only):
+    features (B,C,N) bf16, idx (B,M,K) int32 -> (B,C,M,K) bf16, a bit-exact copy through apb_group_bf16."""
+    _check(features, "features", torch.bfloat16)
+    _check(idx, "idx", torch.int32)
+    B, C, N = features.shape
+    _, M, K = idx.shape
+    out = torch.empty((B, C, M, K), dtype=torch.bfloat16, device=features.device)
+    _cabi.call("apb_group_bf16", [features, idx, out, B, C, N, M, K], features.device)
+    return out
+
+
 def torch_grouping_operation(features, idx):
     """Pure-torch grouping kept for API parity (reference group.py:120-137)."""
     all_idx = idx.reshape(idx.shape[0], -1)

@@ -79,17 +79,17 @@ def tma_ok(x, P):
     return _PRECISION == "tf32" and P % 4 == 0 and x.data_ptr() % 16 == 0
 
 
-def tiny(cin, cout):
+def tiny(cin, cout, P):
     """Layers apb_pwconv_fwd_tf32 computes in exact fp32 on the CUDA cores (csrc/tc_cm_gemm.cu: <= 16 output or <= 8 input
-    channels -- the imitator's mask / probability heads and the xyz embeddings)."""
-    return (cout <= 16 or cin <= 8) and cin * cout * 4 <= 96 * 1024
+    channels, <= 2048 weights, >= 256 points -- the imitator's mask head and the xyz embeddings)."""
+    return (cout <= 16 or cin <= 8) and cin * cout <= 2048 and P >= 256
 
 
 def _gemm_rows(x, w2d, bias, B, cin, cout, P, stats=None):
     """y (B,cout,P) = w2d (cout,cin) . x (B,cin,P) (+bias) through apb_pwconv_fwd_{tf32,bf16}.  The TMA-fed TF32 kernel
     takes any cout in one launch (and can accumulate the BatchNorm statistics of y into `stats` (cout,2) f64); the
     register-staged kernels are called in slices of <= 512 output channels."""
-    if tma_ok(x, P) or (_PRECISION == "tf32" and tiny(cin, cout) and stats is None):
+    if tma_ok(x, P) or (_PRECISION == "tf32" and tiny(cin, cout, P) and stats is None):
         wb, kp = pack_f32(w2d)
         y = torch.empty((B, cout, P), dtype=torch.float32, device=x.device)
         shift = None if bias is None else bias.contiguous().float()
@@ -170,7 +170,7 @@ class PointwiseConvMaxFn(Function):
         cout = weight.shape[0]
         xs = x.detach().contiguous().float().view(B, cin, P)
         w2d = weight.detach().reshape(cout, cin).float()
-        if tma_ok(xs, P) and not tiny(cin, cout):
+        if tma_ok(xs, P) and not tiny(cin, cout, P):
             wb, kp = pack_f32(w2d)
             packed = torch.zeros((B, cout), dtype=torch.int64, device=x.device)
             shift = None if bias is None else bias.detach().contiguous().float()
@@ -240,7 +240,7 @@ def conv_with_stats(mod, x):
     squares of y over (batch, positions) from the GEMM epilogue; stats is None otherwise (caller runs its own pass)."""
     if _use_tc(mod, x):
         P = x[0, 0].numel()
-        if _PRECISION == "tf32" and P % 4 == 0 and not tiny(mod.in_channels, mod.out_channels):
+        if _PRECISION == "tf32" and P % 4 == 0 and not tiny(mod.in_channels, mod.out_channels, P):
             stats = torch.zeros((mod.out_channels, 2), dtype=torch.float64, device=x.device)
             return PointwiseConvFn.apply(x, mod.weight, mod.bias, stats), stats
     return mod(x), None

@@ -150,6 +150,11 @@ def sweep(args, dev, hbm, src, refcuda, flush, B, lines):
                     _cabi.tune_group(0, 0)
                     extra = {"ms_direct_l2_gather": round(ms_d, 4)}
                 emit(f"group_C{C}", ms, mn, 4.0 * B * (C * N + M * K + C * M * K), rms, extra)
+            if "group" in want and C >= 32:     # bf16 features: half the feature bytes, 16-byte stores of eight values
+                fb = feat.to(torch.bfloat16)
+                ms, mn = timeit(lambda: ops.grouping_operation_bf16(fb, nbr), args.iters, flush=flush)
+                emit(f"group_bf16_C{C}", ms, mn, 2.0 * B * (C * N + C * M * K) + 4.0 * B * M * K, None)
+                del fb
             if "group_grad" in want:
                 go = torch.randn(B, C, M, K, device=dev)
                 gp = torch.zeros(B, C, N, device=dev)

@@ -212,6 +212,12 @@ int apb_rowmax_f32(const float *y, float *vmax, int32_t *arg, long long rows, in
 int apb_bnmax_bwd_f32(const float *y, const float *gsel, const int32_t *arg, const float *a, const float *bcoef,
                       float *dy, int B, int C, int M, int K, apb_stream_t stream);
 
+/* grouping_operation on bf16 features (bit-exact copy: out[b,c,j,s] = features[b,c,idx[b,j,s]]), 16-byte stores of
+ * eight bf16 per channel; features (B,C,N), out (B,C,M,K) are bf16 bit patterns.  The bf16 counterpart of
+ * group_points_wrapper (pointnet2_api.cpp:13) for the bf16 shared-MLP path. */
+int apb_group_bf16(const uint16_t *features, const int32_t *idx, uint16_t *out, int B, int C, int N, int M, int K,
+                   apb_stream_t stream);
+
 /* The per-channel arithmetic around BatchNorm -> max over K, in three kernels instead of ~40 element-wise launches:
  *   apb_bnmax_finalize_f32  : (stats (C,2) f64 over `count` elements | NULL = running statistics) -> mean, rstd,
  *                             scale = gamma*rstd, running-statistics update (training), then per (b,c,m):

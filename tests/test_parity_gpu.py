@@ -274,3 +274,20 @@ def test_cpu_tensor_raises():
     from adaptpoint_b200 import _cabi
     with pytest.raises(_cabi.ApbError):
         ops.furthest_point_sample(torch.zeros(1, 8, 3), 2)
+
+
+@pytest.mark.parametrize("B,C,N,M,K", [(4, 32, 1024, 256, 32), (2, 7, 1200, 300, 24), (3, 64, 24000, 6000, 32),
+                                       (1, 5, 100000, 2500, 32), (2, 3, 31, 31, 3), (2, 128, 120000, 1000, 8)])
+def test_group_bf16_bit_exact(cuda_dev, B, C, N, M, K):
+    """apb_group_bf16: a bit-exact copy of the bf16-rounded features, incl. odd sizes (scalar path), rows
+    that fill shared memory (N = 100000) and rows longer than shared memory (direct gather)."""
+    from adaptpoint_b200 import ops
+    gen = torch.Generator().manual_seed(N + C)
+    feat = torch.randn(B, C, N, generator=gen).to(torch.bfloat16).to(cuda_dev)
+    idx = torch.randint(0, N, (B, M, K), generator=gen, dtype=torch.int32).to(cuda_dev)
+    got = ops.grouping_operation_bf16(feat, idx)
+    want = ops.torch_grouping_operation(feat.float(), idx).to(torch.bfloat16)
+    assert torch.equal(got.view(torch.int16), want.view(torch.int16))
+    # and against the fp32 kernel on the same (bf16-representable) values
+    got32 = ops.grouping_operation(feat.float().contiguous(), idx)
+    assert torch.equal(got.float(), got32)
