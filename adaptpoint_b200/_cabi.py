@@ -20,6 +20,7 @@ _d, _ll = ctypes.c_double, ctypes.c_longlong
 _SIGNATURES = {
     "apb_fps_f32": [_p, _p, _p, _i, _i, _i, _p],
     "apb_tune_group": [_i, _i],
+    "apb_tune_wgrad": [_i, _i],
     "apb_tune_group_grad": [_i],
     "apb_tune_group_seg": [_i],
     "apb_gather_f32": [_p, _p, _p, _i, _i, _i, _i, _p],
@@ -41,6 +42,7 @@ _SIGNATURES = {
     "apb_pwconv_ex_tf32": [_p, _p, _p, _p, _i, _p, _i, _p, _p, _i, _i, _i, _i, _i, _p],
     "apb_pmax_decode": [_p, _p, _p, _ll, _p],
     "apb_pwconv_wgrad_tf32": [_p, _p, _p, _i, _i, _i, _i, _p],
+    "apb_pwconv_wgrad_ld_tf32": [_p, _p, _p, _i, _i, _i, _i, _i, _p],
     "apb_affine_f32": [_p, _p, _p, _p, _i, _p, _i, _i, _ll, _p],
     "apb_bn_stats_f32": [_p, _p, _i, _i, _ll, _p],
     "apb_bn_apply_f32": [_p, _p, _p, _p, _f, _d, _i, _p, _p, _p, _p, _p, _f, _i, _i, _ll, _p],

@@ -117,8 +117,7 @@ class SaOneLayerFn(Function):
             if EXACT_GEMM:
                 dwf = torch.einsum("bon,bin->oi", du, fs)
             else:
-                dwf = torch.zeros((C1, cin), dtype=torch.float32, device=dev)
-                _cabi.call("apb_pwconv_wgrad_tf32", [du, fs, dwf, B, cin, C1, N], dev)
+                dwf = tcconv.wgrad(du, fs, B, cin, C1, N)
             dw = torch.cat([(dwp * inv_r).float(), dwf], dim=1).view(wshape)
         # BatchNorm parameter gradients are per-rank sums (the data-parallel all-reduce averages them afterwards)
         return dxyz, dq, df, None, dw, sgx, sg, None, None, None, None, None, None, None, None

@@ -116,6 +116,15 @@ def _gemm_rows(x, w2d, bias, B, cin, cout, P, stats=None):
     return outs[0] if len(outs) == 1 else torch.cat(outs, dim=1)
 
 
+def wgrad(g, x, B, cin, cout, P):
+    """gW (cout, cin) = sum_{b,p} g[b,:,p] x[b,:,p]^T on the TMA-fed TF32 kernel; the accumulator rows are padded to a
+    multiple of 4 floats so that the split-K partial sums land with 128-bit reductions."""
+    ldw = (cin + 3) // 4 * 4
+    gw = torch.zeros((cout, ldw), dtype=torch.float32, device=g.device)
+    _cabi.call("apb_pwconv_wgrad_ld_tf32", [g, x, gw, ldw, B, cin, cout, P], g.device)
+    return gw if ldw == cin else gw[:, :cin].contiguous()
+
+
 class PointwiseConvFn(Function):
     @staticmethod
     def forward(ctx, x, weight, bias, stats=None):
@@ -146,8 +155,7 @@ class PointwiseConvFn(Function):
             gx = _gemm_rows(g, wt, None, B, cout, cin, P).view(shp)
         if ctx.needs_input_grad[1]:
             if P % 4 == 0:
-                gw = torch.zeros((cout, cin), dtype=torch.float32, device=g.device)
-                _cabi.call("apb_pwconv_wgrad_tf32", [g, xs.view(B, cin, P), gw, B, cin, cout, P], g.device)
+                gw = wgrad(g, xs.view(B, cin, P), B, cin, cout, P)
             else:  # TMA needs 16-byte aligned rows; odd point counts do not occur on the PointNeXt path
                 gw = torch.einsum("bop,bip->oi", g, xs.view(B, cin, P))
             gw = gw.view(weight.shape)

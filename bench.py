@@ -101,6 +101,9 @@ def alg_bytes(name, a):
     if name == "apb_sa1_bwd_dense_f32":
         B, N, C = a
         return 4.0 * B * N * (3 * C + 4)
+    if name == "apb_pwconv_wgrad_ld_tf32":
+        _ldw, B, Cin, Cout, P = a
+        return 4.0 * B * P * (Cin + Cout)
     if name == "apb_pwconv_wgrad_tf32":
         B, Cin, Cout, P = a
         return 4.0 * B * P * (Cin + Cout)
@@ -138,7 +141,7 @@ def alg_bytes(name, a):
 
 
 # C-ABI entry points that launch the same kernel are one roofline family
-FAMILY = {"apb_pwconv_ex_tf32": "apb_pwconv_fwd_tf32"}
+FAMILY = {"apb_pwconv_ex_tf32": "apb_pwconv_fwd_tf32", "apb_pwconv_wgrad_ld_tf32": "apb_pwconv_wgrad_tf32"}
 
 
 class ClockSampler:

@@ -53,6 +53,7 @@ int apb_fps_f32(const float *xyz, float *temp, int32_t *idx, int B, int N, int m
 /* Benchmarks only: override the forward grouping/gather work split (channels staged per CTA in
  * {0,1,2,4}, threads per CTA in {0,256,512,1024}; 0 = automatic; channels -1 = rows longer than shared
  * memory use the direct L2 gather instead of the cluster kernel).  No reference counterpart. */
+int apb_tune_wgrad(int force_mt, int min_chunks);
 int apb_tune_group(int channels_per_cta, int threads);
 /* Benchmarks only: backward path of grouping / three_interpolate: 0 = automatic, 1 = scattered L2
  * reductions (the reference's scheme), 2 = accumulator rows in shared memory.  No reference counterpart. */
@@ -161,6 +162,10 @@ int apb_pmax_decode(const unsigned long long *packed, float *val, int32_t *arg, 
  * The data gradient is apb_pwconv_fwd_bf16 on grad_y with the transposed weights. */
 int apb_pwconv_wgrad_tf32(const float *grad_y, const float *x, float *grad_w, int B, int Cin, int Cout, int P,
                           apb_stream_t stream);
+/* Same with a row pitch ldw >= Cin for grad_w (Cout, ldw): with ldw % 4 == 0 the split-K partial sums are added with
+ * 128-bit reductions (4 columns per instruction) instead of scalar atomics; columns Cin .. ldw-1 receive zeros. */
+int apb_pwconv_wgrad_ld_tf32(const float *grad_y, const float *x, float *grad_w, int ldw, int B, int Cin, int Cout,
+                             int P, apb_stream_t stream);
 
 /* Fused set-abstraction aggregation for BatchNorm-folded blocks: group -> relative position (/radius) ->
  * shared MLP (1 or 2 layers) -> max over the K neighbours, without materialising any (B,C,M,K) tensor.

@@ -1,0 +1,5 @@
+set -x
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests -q -m gpu > gpurun_out/r02_k_tests.log 2>&1; echo "tests exit $?"; grep -E "passed|failed" gpurun_out/r02_k_tests.log | tail -2; grep -E "^FAILED|^ERROR|^E  " gpurun_out/r02_k_tests.log | cut -c1-300 | head -20
+timeout 400 python bench.py --steps 20 --warmup 5 --no-cpu --dump-kernels gpurun_out/kernels_r02_k.json > gpurun_out/bench_r02_k.json 2> gpurun_out/bench_r02_k.err; echo "bench exit $?"; cut -c1-240 gpurun_out/bench_r02_k.json; tail -3 gpurun_out/bench_r02_k.err
+timeout 300 python benchmarks/bench_models.py --steps 10 --warmup 3 --cases b-cls,xl-seg > gpurun_out/models_r02_k_n1.jsonl 2> gpurun_out/models_r02_k.err; echo "models exit $?"; cut -c1-260 gpurun_out/models_r02_k_n1.jsonl; tail -2 gpurun_out/models_r02_k.err
