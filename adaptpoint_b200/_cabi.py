@@ -51,6 +51,10 @@ _SIGNATURES = {
     "apb_kmax_stats_f32": [_p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
     "apb_attn_fwd_f32": [_p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
     "apb_attn_bwd_f32": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
+    "apb_spectral_norm_fwd_f32": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _f, _i, _i, _p],
+    "apb_spectral_norm_bwd_f32": [_p, _p, _p, _p, _p, _p, _p, _i, _i, _p],
+    "apb_bn_fold_f32": [_p, _p, _p, _p, _f, _p, _p, _p, _i, _p],
+    "apb_sums_split_f32": [_p, _p, _p, _i, _p],
     "apb_bnmax_finalize_f32": [_p, _d, _f, _f, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _p, _p, _p, _i, _i, _i, _p],
     "apb_bnmax_bwd_reduce_f32": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _p],
     "apb_bnmax_bwd_coef_f32": [_p, _p, _p, _p, _p, _d, _p, _p, _p, _p, _i, _p],

@@ -755,3 +755,42 @@ extern "C" int apb_bnmax_bwd_coef_f32(const double *tot, const double *local, co
     APB_CHECK_LAUNCH();
     return APB_OK;
 }
+
+// ---- eval-mode fold and small conversions: one launch instead of 4-5 element-wise ones per BatchNorm layer ------------
+__global__ void bn_fold_kernel(const float *__restrict__ gamma, const float *__restrict__ beta,
+                               const float *__restrict__ mean, const float *__restrict__ var, float eps,
+                               float *__restrict__ scale, float *__restrict__ shift, float *__restrict__ rstd, int C) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const float r = rsqrtf(var[c] + eps);
+    const float s = gamma[c] * r;
+    rstd[c] = r;
+    scale[c] = s;
+    shift[c] = beta[c] - mean[c] * s;
+}
+
+__global__ void sums_split_kernel(const double *__restrict__ sums, float *__restrict__ first, float *__restrict__ second,
+                                  int C) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    first[c] = (float)sums[2 * c];
+    second[c] = (float)sums[2 * c + 1];
+}
+
+extern "C" int apb_bn_fold_f32(const float *gamma, const float *beta, const float *running_mean, const float *running_var,
+                               float eps, float *scale, float *shift, float *rstd, int C, apb_stream_t stream) {
+    if (C <= 0) return APB_E_INVALID;
+    if (!gamma || !beta || !running_mean || !running_var || !scale || !shift || !rstd) return APB_E_INVALID;
+    bn_fold_kernel<<<apb_div_up(C, 128), 128, 0, (cudaStream_t)stream>>>(gamma, beta, running_mean, running_var, eps, scale,
+                                                                         shift, rstd, C);
+    APB_CHECK_LAUNCH();
+    return APB_OK;
+}
+
+extern "C" int apb_sums_split_f32(const double *sums, float *first, float *second, int C, apb_stream_t stream) {
+    if (C <= 0) return APB_E_INVALID;
+    if (!sums || !first || !second) return APB_E_INVALID;
+    sums_split_kernel<<<apb_div_up(C, 128), 128, 0, (cudaStream_t)stream>>>(sums, first, second, C);
+    APB_CHECK_LAUNCH();
+    return APB_OK;
+}

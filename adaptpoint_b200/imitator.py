@@ -25,6 +25,7 @@ from torch.autograd import Function
 
 from . import _cabi, geometry, ops
 from .norm import ConvBlock, TcBatchNorm1d
+from .spectral import spectral_norm
 from .tcconv import TcConv1d, TcConv2d, conv_max
 
 
@@ -371,7 +372,7 @@ class PointNetSetAbstraction_SpectralNorm(nn.Module):
         self.mlp_bns = nn.ModuleList()
         last = in_channel
         for out in mlp:
-            self.mlp_convs.append(nn.utils.parametrizations.spectral_norm(TcConv2d(last, out, 1)))
+            self.mlp_convs.append(spectral_norm(TcConv2d(last, out, 1)))
             last = out
         self.group_all = group_all
 
@@ -389,7 +390,7 @@ class PointNetSetAbstraction_SpectralNorm(nn.Module):
 class PointDiscriminator1(nn.Module):
     def __init__(self, num_classes=40, normal_channel=False, **kwargs):
         super().__init__()
-        sn = nn.utils.parametrizations.spectral_norm
+        sn = spectral_norm
         self.normal_channel = normal_channel
         self.sa1 = PointNetSetAbstraction_SpectralNorm(None, None, None, in_channel=3, mlp=[64, 128, 1024],
                                                        group_all=True)

@@ -83,7 +83,9 @@ class BatchNormActFn(Function):
             _cabi.call("apb_bn_bwd_apply_f32", [xs, g, y, save_mean, save_rstd, weight, stats2, ctx.count, dx, B, C, P],
                        dev)
         # parameter gradients are per-rank sums (the data-parallel all-reduce averages them afterwards)
-        return dx, local[:, 1].float(), local[:, 0].float(), None, None, None, None, None, None, None
+        dbeta, dgamma = torch.empty_like(save_mean), torch.empty_like(save_mean)
+        _cabi.call("apb_sums_split_f32", [local, dbeta, dgamma, C], dev)
+        return dx, dgamma, dbeta, None, None, None, None, None, None, None
 
 
 class BatchNormEvalFn(Function):
@@ -94,9 +96,9 @@ class BatchNormEvalFn(Function):
     def forward(ctx, x, weight, bias, running_mean, running_var, eps, relu):
         xs = x.contiguous()
         B, C, P = _dims(xs)
-        rstd = torch.rsqrt(running_var.float() + eps)
-        scale = (weight * rstd).contiguous()
-        shift = (bias - running_mean * scale).contiguous()
+        scale, shift, rstd = (torch.empty(C, dtype=torch.float32, device=xs.device) for _ in range(3))
+        _cabi.call("apb_bn_fold_f32", [weight.detach(), bias.detach(), running_mean, running_var, float(eps), scale, shift,
+                                       rstd, C], xs.device)
         y = torch.empty_like(xs)
         _cabi.call("apb_affine_f32", [xs, None, scale, shift, int(relu), y, B, C, P], xs.device)
         need_param_grads = weight.requires_grad or bias.requires_grad
@@ -116,9 +118,9 @@ class BatchNormEvalFn(Function):
             _cabi.call("apb_affine_f32", [g, y, scale, None, 0, dx, B, C, P], dev)
         if (ctx.needs_input_grad[1] or ctx.needs_input_grad[2]) and xs is not None:
             stats2 = torch.zeros((C, 2), dtype=torch.float64, device=dev)
-            _cabi.call("apb_bn_bwd_reduce_f32", [xs, g, y, mean.float().contiguous(), rstd.contiguous(), stats2,
-                                                 B, C, P], dev)
-            dgamma, dbeta = stats2[:, 1].float(), stats2[:, 0].float()
+            _cabi.call("apb_bn_bwd_reduce_f32", [xs, g, y, mean, rstd, stats2, B, C, P], dev)
+            dbeta, dgamma = torch.empty_like(rstd), torch.empty_like(rstd)
+            _cabi.call("apb_sums_split_f32", [stats2, dbeta, dgamma, C], dev)
         return dx, dgamma, dbeta, None, None, None, None
 
 

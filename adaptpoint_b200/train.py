@@ -291,7 +291,17 @@ class AdaptPointTrainer:
         fake_label = torch.full((B, 1), 0.1, device=inp.device)
 
         _, gen = G(inp, noise.get("gen"))
-        g_loss_raw = self.criterion_gan(D(gen), real_label)
+        # The discriminator only relays gradients to the imitator here: its own parameter gradients from this pass are
+        # discarded by `optimizer_D.zero_grad()` (train_autoaug.py:183) before they are ever used, so they are not computed
+        # (same reasoning as for the classifier below).
+        dparams = [p for p in D.parameters() if p.requires_grad]
+        for p in dparams:
+            p.requires_grad_(False)
+        try:
+            g_loss_raw = self.criterion_gan(D(gen), real_label)
+        finally:
+            for p in dparams:
+                p.requires_grad_(True)
         fake_pts = torch.cat([gen, points[:, :, 3:]], dim=-1)   # `points[:, :, :3] = gen_imgs` (:152)
         data_fake = {"pos": fake_pts[:, :, :3].contiguous(), "y": label,
                      "x": fake_pts[:, :, :nc].transpose(1, 2).contiguous()}

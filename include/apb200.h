@@ -223,6 +223,23 @@ int apb_bnmax_bwd_f32(const float *y, const float *gsel, const int32_t *arg, con
 int apb_group_bf16(const uint16_t *features, const int32_t *idx, uint16_t *out, int B, int C, int N, int M, int K,
                    apb_stream_t stream);
 
+/* Spectral normalisation with one power iteration (torch.nn.utils.parametrizations.spectral_norm in training mode, as
+ * used by PointDiscriminator1, openpoints/models_adaptpoint/point_discriminator.py:23-34): w_mat (h,w) row-major,
+ * u (h), v (w) updated in place; t_ws (h) workspace; scratch (4+w) f32 pre-zeroed; u_saved, v_saved, sigma (1), w_sn (h,w)
+ * outputs: w_sn = w_mat / sigma with sigma = u^T w_mat v.  3 launches.  Backward (u, v constant, as in torch):
+ * grad_w = (grad - <grad, w_sn> u v^T) / sigma, scratch (4) f32 pre-zeroed, 2 launches. */
+int apb_spectral_norm_fwd_f32(const float *w_mat, float *u, float *v, float *t_ws, float *scratch, float *u_saved,
+                              float *v_saved, float *sigma, float *w_sn, float eps, int h, int w, apb_stream_t stream);
+int apb_spectral_norm_bwd_f32(const float *grad, const float *w_sn, const float *u_saved, const float *v_saved,
+                              const float *sigma, float *scratch, float *grad_w, int h, int w, apb_stream_t stream);
+
+/* Eval-mode BatchNorm fold (scale = gamma*rsqrt(var+eps), shift = beta - mean*scale, rstd) and the split of a (C,2)
+ * f64 sum pair into two f32 vectors: one launch each instead of the 4-5 element-wise launches torch would issue per
+ * BatchNorm layer (openpoints/models/layers/norm.py:57-71 in eval mode / its parameter gradients). */
+int apb_bn_fold_f32(const float *gamma, const float *beta, const float *running_mean, const float *running_var, float eps,
+                    float *scale, float *shift, float *rstd, int C, apb_stream_t stream);
+int apb_sums_split_f32(const double *sums, float *first, float *second, int C, apb_stream_t stream);
+
 /* The per-channel arithmetic around BatchNorm -> max over K, in three kernels instead of ~40 element-wise launches:
  *   apb_bnmax_finalize_f32  : (stats (C,2) f64 over `count` elements | NULL = running statistics) -> mean, rstd,
  *                             scale = gamma*rstd, running-statistics update (training), then per (b,c,m):
