@@ -252,6 +252,10 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device (adaptpoint_b200 has no CPU product path)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    # stdout carries exactly ONE JSON line: libraries that print there (NCCL's version banner at N > 1) go to stderr
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     torch.backends.cudnn.allow_tf32 = False            # strict fp32 in the library GEMMs/convs ("dtype": "f32")
     torch.backends.cuda.matmul.allow_tf32 = False
     if world > 1:
@@ -418,8 +422,13 @@ def run_ours(args):
                 json.dump([{"call": k[0], "dims": list(k[1]), "launches": v[0], "ms_total": round(v[1], 4),
                             "us_per_launch": round(v[1] * 1e3 / max(v[0], 1), 2),
                             "alg_bytes_per_launch": alg_bytes(k[0], k[1])} for k, v in table], f, indent=1)
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
         print(json.dumps(out), flush=True)
+        os.dup2(2, 1)
     teardown(tr, world)
+    sys.stdout.flush()
+    os.dup2(real_stdout, 1)
 
 
 def teardown(tr, world):

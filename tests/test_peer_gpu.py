@@ -1,5 +1,6 @@
-"""Peer-memory all-reduce (csrc/peer.cu) against NCCL on the same buffers; needs >= 2 GPUs of one node (skipped on
-the 1-GPU box).  Also run by scripts/gpu_r01_u.sh on a 2-GPU box."""
+"""Peer-memory all-reduce (csrc/peer.cu) against NCCL on the same buffers, on EVERY GPU of the box (2, 4 or 8 ranks; skipped
+on a 1-GPU box): equality with NCCL, CUDA-graph replay, and calls issued from two streams without host synchronisation
+(peer.py orders them with events: the workspace has one sequence counter).  Run by scripts/gpu_r02_scale.sh."""
 import os
 import sys
 
@@ -46,6 +47,15 @@ def _worker(rank, world, port, out):
     torch.cuda.synchronize()
     expect = float(sum(r + 1 for r in range(world)) * world)
     graph_ok = bool((buf == expect).all())
+    # two streams, no host sync between the calls: the guard in peer.py must serialise them
+    sa, sb = torch.cuda.Stream(), torch.cuda.Stream()
+    xs = [torch.full((64,), float(rank + 1 + i), device=dev, dtype=torch.float64) for i in range(20)]
+    torch.cuda.synchronize()
+    for i, x in enumerate(xs):
+        with torch.cuda.stream(sa if i % 2 == 0 else sb):
+            ctx.allreduce_(x)
+    torch.cuda.synchronize()
+    streams_ok = all(bool((x == float(sum(r + 1 + i for r in range(world)))).all()) for i, x in enumerate(xs))
     # latency against NCCL on a (128,2) f64 statistic
     st = torch.zeros(256, device=dev, dtype=torch.float64)
     res = {}
@@ -62,7 +72,7 @@ def _worker(rank, world, port, out):
         torch.cuda.synchronize()
         res[name] = e0.elapsed_time(e1) / 200 * 1e3
     if rank == 0:
-        torch.save({"worst_rel": worst, "graph_ok": graph_ok, "us": res}, out)
+        torch.save({"worst_rel": worst, "graph_ok": graph_ok, "streams_ok": streams_ok, "us": res, "world": world}, out)
     dist.barrier()
     torch.cuda.synchronize()
     os._exit(0)
@@ -80,9 +90,11 @@ def run(world=2, port=29533, out="/tmp/apb_peer_test.pt"):
 def test_peer_allreduce_matches_nccl():
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs on one node")
-    r = run()
+    r = run(world=min(torch.cuda.device_count(), 8))
+    print("peer all-reduce:", r)
     assert r["worst_rel"] < 1e-12 or r["worst_rel"] < 1e-6, r      # f64 sums exact up to order; f32 within 1e-6
     assert r["graph_ok"], r
+    assert r["streams_ok"], r
 
 
 if __name__ == "__main__":
