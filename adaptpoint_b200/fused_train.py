@@ -24,6 +24,13 @@ ENABLED = os.environ.get("APB_NO_FUSED_TRAIN", "0") != "1"
 # compared element by element with the unfused fp32 op sequence (TF32 noise flips a fraction of the max-over-K routes,
 # which moves whole gradient entries between support points).
 EXACT_GEMM = False
+# Per-step cache of the idx-only backward statistics (cnt, sdp, moments): the InvResMLP blocks of a stage share one
+# ball-query result (geometry.ball_query memo), so apb_sa1_bwd_count_f32 runs once per distinct idx per step.
+_CNT = {}
+
+
+def reset_step_cache():
+    _CNT.clear()
 
 
 def usable(mod, grouper, convs, feature_type, reduction, query_p, p, f):
@@ -100,10 +107,16 @@ class SaOneLayerFn(Function):
         dq = torch.zeros_like(qs) if ctx.needs_input_grad[1] else None
         _cabi.call("apb_sa1_bwd_sparse_f32", [gs, ksel, idx, ps, qs, wp, du, dwp, dxyz, dq, B, N, M, K, C1], dev)
         if training:
-            cnt = torch.zeros((B, N), dtype=torch.float32, device=dev)
-            sdp = torch.zeros((B, N, 3), dtype=torch.float32, device=dev)
-            mom = torch.zeros(12, dtype=torch.float64, device=dev)
-            _cabi.call("apb_sa1_bwd_count_f32", [ps, qs, idx, cnt, sdp, mom, B, N, M, K], dev)
+            key = (idx.data_ptr(), tuple(idx.shape), ps.data_ptr(), qs.data_ptr())
+            hit = _CNT.get(key)
+            if hit is None:
+                cnt = torch.zeros((B, N), dtype=torch.float32, device=dev)
+                sdp = torch.zeros((B, N, 3), dtype=torch.float32, device=dev)
+                mom = torch.zeros(12, dtype=torch.float64, device=dev)
+                _cabi.call("apb_sa1_bwd_count_f32", [ps, qs, idx, cnt, sdp, mom, B, N, M, K], dev)
+                _CNT[key] = (cnt, sdp, mom, idx)     # idx kept alive: its address identifies the entry
+            else:
+                cnt, sdp, mom, _ = hit
             usdp = torch.zeros((C1, 3), dtype=torch.float64, device=dev)
             _cabi.call("apb_sa1_bwd_dense_f32", [u, cnt, sdp, a, bcoef, wp, du, usdp, B, N, C1], dev)
             if need_w:

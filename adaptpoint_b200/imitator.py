@@ -223,7 +223,7 @@ class Anchor_selfattention(nn.Module):
         q, k, v = self.to_qkv(x).chunk(3, dim=-1)
         if x.is_cuda:      # our fp32 kernels (flash-style for head_dim 16, few-token otherwise), token-major in / out
             o = ops.self_attention(q + emb, k + emb, v + emb, self.head_num)
-        else:              # CPU tensors only: the oracle-patched tests and the CPU baseline of bench.py
+        else:              # CPU tensors only: the op-patched CPU tests and the CPU baseline of bench.py
             split = lambda t: (t + emb).reshape(B, M, self.head_num, self.head_dim).permute(0, 2, 1, 3)
             o = F.scaled_dot_product_attention(split(q), split(k), split(v))
             o = o.permute(0, 2, 1, 3).reshape(B, M, -1)

@@ -301,10 +301,37 @@ class PointNextEncoder(nn.Module):
                                     expansion=self.expansion, use_res=self.use_res, fused=self.fused))
         return nn.Sequential(*layers)
 
+    def geometry_spec(self, n):
+        """(chains, queries) of one forward over n-point clouds, in geometry.SamplingPlan / GeometryMailbox terms: the
+        FPS chain of the strided stages, the ball query of every stage-opening SetAbstraction (support = parent level)
+        and the one query the InvResMLP blocks of a stage share (the level querying itself)."""
+        chain, queries, path = [], [], ()
+        for stage in self.encoder:
+            sa = stage[0]
+            if getattr(sa, "stride", 1) > 1 and not sa.is_head:
+                n = n // sa.stride
+                child = path + (n,)
+                chain.append(n)
+                g = sa.grouper
+                if getattr(g, "radius", None) is not None and getattr(g, "nsample", None) is not None:
+                    queries.append((path, child, float(g.radius), int(g.nsample)))
+                path = child
+            for blk in list(stage)[1:]:
+                g = getattr(getattr(blk, "convs", None), "grouper", None)
+                if getattr(g, "radius", None) is not None and getattr(g, "nsample", None) is not None:
+                    q = (path, path, float(g.radius), int(g.nsample))
+                    if q not in queries:
+                        queries.append(q)
+        return [chain], queries
+
     @staticmethod
     def _unpack(p0, f0):
         if hasattr(p0, "keys"):
             p0, f0 = p0["pos"], p0.get("x", None)
+        if hasattr(p0, "__dict__"):
+            p0.__dict__.pop("_apb_bq", None)     # the ball-query memo (geometry.ball_query) lives for ONE forward
+        from . import fused_train
+        fused_train.reset_step_cache()
         if f0 is None:
             f0 = p0.clone().transpose(1, 2).contiguous()
         return p0, f0

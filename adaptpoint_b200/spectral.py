@@ -4,7 +4,7 @@ Drop-in for torch.nn.utils.parametrizations.spectral_norm as PointDiscriminator1
 (openpoints/models_adaptpoint/point_discriminator.py:23-34): same parametrization class hierarchy, same state_dict entries
 (`parametrizations.weight.original`, `parametrizations.weight.0._u`, `._v`), same semantics -- one power iteration per
 training-mode forward that updates u, v in place, sigma = u^T W v with u, v treated as constants by autograd.  On CUDA
-fp32 weights in training mode the arithmetic runs in `SpectralNormFn`; everything else (CPU tensors of the oracle-patched
+fp32 weights in training mode the arithmetic runs in `SpectralNormFn`; everything else (CPU tensors of the op-patched
 tests, eval mode, exotic settings) takes torch's own implementation.
 """
 import torch

@@ -9,7 +9,7 @@ backend switch is "tc", run
     gW = gy x^T              apb_pwconv_wgrad_tf32 (TF32, both operands TMA-fed)
 Numerics: tf32 (default) ~1e-3 relative per layer; bf16 2e-2 (BASELINE.json north_star, "bf16 MLP path").  "tc" is
 the product path and the default for CUDA tensors; the switch at "torch" turns the layers back into plain
-nn.Conv{1,2}d -- a TEST-ONLY strict-fp32 mode (tests/, the golden parity runs); CPU tensors (the oracle-patched CPU
+nn.Conv{1,2}d -- a TEST-ONLY strict-fp32 mode (tests/, the golden parity runs); CPU tensors (the op-patched CPU
 tests and the CPU baseline of bench.py) always take the nn.Conv path, there is no CPU product path.
 """
 import contextlib

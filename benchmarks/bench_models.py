@@ -61,16 +61,34 @@ def run_case(name, args, rank, world, dev):
     opt = torch.optim.AdamW(params, lr=1e-3, weight_decay=1e-4, fused=True, capturable=args.graph)
     pos, x, y = make_batch(B, N, classes, seg, 100 + rank, dev)
 
+    # Geometry prefetch (geometry.GeometryMailbox): FPS is strictly sequential (6000 rounds for 24000 -> 6000) and needs
+    # coordinates only, so the FPS / ball-query chain of the NEXT batch runs on a side stream beside the backward pass of
+    # the current one, as a loader-driven training loop would arrange it.  Every step still executes one full chain
+    # inside the timed region (for the batch after it); --no-prefetch keeps it inline in the forward pass.
+    mailbox = None
+    if args.prefetch:
+        from adaptpoint_b200 import geometry
+        geo = torch.cuda.Stream(device=dev)
+        mailbox = geometry.GeometryMailbox(*model.encoder.geometry_spec(N), geo)
+        mailbox.prefetch(pos)
+        torch.cuda.current_stream(dev).wait_stream(geo)
+
     def step():
         opt.zero_grad(set_to_none=True)
         with tcconv.conv_backend(args.conv):   # 'tc': 1x1 convs (fwd, dgrad, wgrad) on libapb200's tcgen05 kernels
+            if mailbox is not None:
+                mailbox.attach(pos)
             if seg:
                 loss = torch.nn.functional.cross_entropy(model({"pos": pos, "x": x}), y)
             else:
                 _, loss = model.get_logits_loss({"pos": pos, "x": x}, y)
+            if mailbox is not None:
+                mailbox.prefetch(pos)          # the next batch (synthetic: the same clouds) -- beside the backward pass
             loss.backward()
         allreduce_grads(params)
         opt.step()
+        if mailbox is not None:
+            torch.cuda.current_stream(dev).wait_stream(mailbox.stream)
         return loss
 
     def barrier():
@@ -78,6 +96,29 @@ def run_case(name, args, rank, world, dev):
             dist.barrier()
         torch.cuda.synchronize()
 
+    if args.dump_kernels and rank == 0:       # per C-ABI call CUDA-event trace of two eager steps (host-launch skew included)
+        from adaptpoint_b200 import _cabi
+        for _ in range(2):
+            step()
+        torch.cuda.synchronize()
+        _cabi.TRACE = []
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(2):
+            step()
+        e1.record()
+        torch.cuda.synchronize()
+        trace, _cabi.TRACE = _cabi.TRACE, None
+        agg = {}
+        for nm, a, a0, a1 in trace:
+            d = agg.setdefault(nm, [0, 0.0])
+            d[0] += 1
+            d[1] += a0.elapsed_time(a1)
+        rows = sorted(({"call": k, "launches_per_step": v[0] // 2, "ms_per_step": round(v[1] / 2, 3)} for k, v in agg.items()),
+                      key=lambda r: -r["ms_per_step"])
+        with open(f"{args.dump_kernels}.{name}.json", "w") as f:
+            json.dump({"eager_ms_per_step": round(e0.elapsed_time(e1) / 2, 3), "ours_ms_per_step": round(sum(r["ms_per_step"] for r in rows), 3),
+                       "calls": rows}, f, indent=1)
     graph = None
     if args.graph:
         eager_step = step
@@ -125,6 +166,7 @@ def run_case(name, args, rank, world, dev):
             "params_m": round(sum(p.numel() for p in params) / 1e6, 3),
             "config": {"workload": f"{key} fwd+bwd+allreduce+AdamW, B={B}/GPU, N={N}, {classes} classes, "
                                    f"{'one CUDA graph' if args.graph else 'eager'}, "
+                                   f"geometry {'of the next batch prefetched beside the backward pass' if args.prefetch else 'inline'}, "
                                    f"1x1 convs: {'libapb200 tcgen05 tf32' if args.conv == 'tc' else 'cuDNN fp32'}",
                        "parallelism": f"dp{world}"}}), flush=True)
     if graph is not None:                      # a graph holding NCCL work must go before destroy_process_group
@@ -146,6 +188,9 @@ def main():
     ap.add_argument("--eager", dest="graph", action="store_false", help="launch the step kernel by kernel instead of "
                     "replaying one CUDA graph")
     ap.add_argument("--graph", dest="graph", action="store_true", help="(default) capture the step in one CUDA graph")
+    ap.add_argument("--dump-kernels", default="", help="prefix of per-case JSON files with a per-C-ABI-call time table")
+    ap.add_argument("--no-prefetch", dest="prefetch", action="store_false", help="FPS / ball queries inline in the "
+                    "forward pass instead of one step ahead on a side stream")
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch override (default: SURVEY 8d's 32 / 32 / 8)")
     ap.set_defaults(graph=True)
     args = ap.parse_args()

@@ -1,3 +1,3 @@
 set -x
 mkdir -p gpurun_out
-timeout 300 python scripts/dbg_sn.py > gpurun_out/r02_c_dbg.log 2>&1; echo "dbg exit $?"; grep -v Warning gpurun_out/r02_c_dbg.log | tail -12
+timeout 300 python -m pytest tests/test_geometry_gpu.py -q 2>&1 | tail -12 | cut -c1-300
