@@ -72,6 +72,11 @@ class GatherOperation(Function):
 gather_operation = GatherOperation.apply
 
 
+# Support clouds of at least this many points go through the cell grid (below it the tiled O(M*N) kernel is as fast: its
+# whole cloud sits in one or two shared-memory tiles and the grid costs four small build launches).
+BALL_QUERY_GRID_MIN_N = 4096
+
+
 class BallQuery(Function):
     @staticmethod
     def forward(ctx, radius: float, nsample: int, xyz: torch.Tensor, new_xyz: torch.Tensor) -> torch.Tensor:
@@ -82,7 +87,14 @@ class BallQuery(Function):
         B, N, _ = xyz.size()
         npoint = new_xyz.size(1)
         idx = torch.empty((B, npoint, nsample), dtype=torch.int32, device=xyz.device)
-        _cabi.call("apb_ball_query_f32", [new_xyz, xyz, idx, B, N, npoint, float(radius), int(nsample)], xyz.device)
+        if N >= BALL_QUERY_GRID_MIN_N and 0 < nsample <= 96 and B <= 65535:
+            # cell-grid kernel (csrc/query_grid.cu): same rows bit for bit, O(M * neighbourhood) pair evaluations
+            nbytes = _cabi.load().apb_ball_query_grid_ws_bytes(B, N)
+            ws = torch.empty(nbytes, dtype=torch.uint8, device=xyz.device)
+            _cabi.call("apb_ball_query_grid_f32", [new_xyz, xyz, idx, ws, nbytes, B, N, npoint, float(radius),
+                                                   int(nsample)], xyz.device)
+        else:
+            _cabi.call("apb_ball_query_f32", [new_xyz, xyz, idx, B, N, npoint, float(radius), int(nsample)], xyz.device)
         ctx.mark_non_differentiable(idx)
         return idx
 

@@ -67,6 +67,9 @@ def alg_bytes(name, a):
     if name == "apb_ball_query_f32":
         B, N, M, K = a
         return 4.0 * B * (3 * N + 3 * M + M * K)
+    if name == "apb_ball_query_grid_f32":
+        _ws, B, N, M, K = a
+        return 4.0 * B * (3 * N + 3 * M + M * K)
     if name == "apb_knn_f32":
         B, N, M, K = a
         return 4.0 * B * (3 * N + 3 * M + 2 * M * K)

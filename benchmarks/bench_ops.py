@@ -117,8 +117,14 @@ def sweep(args, dev, hbm, src, refcuda, flush, B, lines):
             rms = None
             if refcuda is not None:
                 rms, _ = timeit(lambda: refcuda.ball_query(0.1, K, xyz, new_xyz), max(2, args.iters // 2), warm=1)
+            from adaptpoint_b200 import _cabi as _c
+            tiled = torch.empty_like(nbr)
+            tms, _ = timeit(lambda: _c.call("apb_ball_query_f32", [new_xyz, xyz, tiled, B, N, M, 0.1, K], dev),
+                            max(2, args.iters // 2), flush=flush)
             emit("ball_query", ms, mn, 4.0 * B * (3 * N + 3 * M + M * K), rms,
-                 {"pairs_upper": B * M * N, "Tpairs_per_s_upper": round(B * M * N / (ms / 1e3) / 1e12, 3)})
+                 {"pairs_upper": B * M * N, "Tpairs_per_s_upper": round(B * M * N / (ms / 1e3) / 1e12, 3),
+                  "kernel": "cell grid" if N >= ops.BALL_QUERY_GRID_MIN_N else "tiled O(M*N)",
+                  "tiled_kernel_ms": round(tms, 4), "bit_equal_to_tiled": bool(torch.equal(tiled, nbr))})
         for C in (3, 32, 128):
             if C * B * M * K * 4 > 24e9:
                 continue

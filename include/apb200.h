@@ -75,6 +75,13 @@ int apb_gather_grad_f32(const float *grad_out, const int32_t *idx, float *grad_p
  * zeros, which is what the reference's pre-zeroed buffer holds). */
 int apb_ball_query_f32(const float *new_xyz, const float *xyz, int32_t *idx, int B, int N, int M,
                        float radius, int nsample, apb_stream_t stream);
+/* The same query through a uniform cell grid built per call (csrc/query_grid.cu): O(M * neighbourhood) instead of
+ * O(M * N) distance evaluations, bit-identical rows (the nsample smallest in-radius indices == the first nsample in
+ * index order).  workspace: apb_ball_query_grid_ws_bytes(B, N) bytes of device memory, 256-byte aligned, contents
+ * irrelevant; nsample <= 96. */
+long long apb_ball_query_grid_ws_bytes(int B, int N);
+int apb_ball_query_grid_f32(const float *new_xyz, const float *xyz, int32_t *idx, void *workspace, long long ws_bytes,
+                            int B, int N, int M, float radius, int nsample, apb_stream_t stream);
 
 /* kNN over squared distances, order (distance, index) ascending.  Replaces KNN.forward =
  * torch.cdist + topk in group.py:12-28 (no native function in the reference).

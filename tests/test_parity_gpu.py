@@ -291,3 +291,41 @@ def test_group_bf16_bit_exact(cuda_dev, B, C, N, M, K):
     # and against the fp32 kernel on the same (bf16-representable) values
     got32 = ops.grouping_operation(feat.float().contiguous(), idx)
     assert torch.equal(got.float(), got32)
+
+
+@pytest.mark.parametrize("B,N,M,radius,K,kind", [(4, 16384, 4096, 0.1, 32, "shell"), (2, 24000, 6000, 0.1, 32, "ball"),
+                                                 (2, 6000, 6000, 0.2, 32, "ball"), (3, 5000, 1250, 0.05, 16, "quant"),
+                                                 (2, 4096, 4096, 0.8, 24, "ball"), (2, 4100, 1000, 0.15, 64, "dup"),
+                                                 (1, 100000, 25000, 0.1, 32, "shell"), (2, 4096, 512, 0.1, 32, "same"),
+                                                 (2, 8192, 2048, 0.0, 8, "ball"), (2, 8192, 2048, 3.0, 96, "ball")])
+def test_ball_query_grid_bit_exact(cuda_dev, B, N, M, radius, K, kind):
+    """csrc/query_grid.cu (cell grid, nsample smallest in-radius indices) against the tiled index-order kernel and, at
+    sizes the C oracle finishes quickly, against the oracle: identical rows on shells, balls, quantised coordinates
+    (exact distance ties at the radius), duplicated points, an all-identical cloud, radius 0 and a radius that covers
+    the whole cloud, queries that are / are not a subset of the support set."""
+    from adaptpoint_b200 import _cabi, ops
+    from adaptpoint_b200.synth import make_clouds
+    gen = torch.Generator().manual_seed(N + K)
+    if kind in ("shell", "ball"):
+        xyz = make_clouds(B, N, kind, 5)
+    elif kind == "quant":
+        xyz = (make_clouds(B, N, "ball", 6) * 64).round() / 64
+    elif kind == "dup":
+        xyz = make_clouds(B, N, "ball", 7)
+        xyz[:, N // 2:] = xyz[:, :N - N // 2]
+    else:
+        xyz = torch.full((B, N, 3), 0.25)
+    if kind in ("ball", "quant") and M != N:
+        q = torch.rand(B, M, 3, generator=gen) * 2.4 - 1.2          # queries outside the support's bounding box too
+    else:
+        sel = torch.stack([torch.randperm(N, generator=gen)[:M] for _ in range(B)])
+        q = torch.gather(xyz, 1, sel.unsqueeze(-1).expand(-1, -1, 3)).contiguous()
+    xd, qd = xyz.to(cuda_dev), q.to(cuda_dev)
+    assert N >= ops.BALL_QUERY_GRID_MIN_N
+    got = ops.ball_query(radius, K, xd, qd)
+    want = torch.empty_like(got)
+    _cabi.call("apb_ball_query_f32", [qd, xd, want, B, N, M, float(radius), K], cuda_dev)
+    assert torch.equal(got, want)
+    if N * M * B <= 3e8:
+        from oracle import cpu as orc
+        assert np.array_equal(got.cpu().numpy(), orc.ball_query(radius, K, xyz.numpy(), q.numpy()))
