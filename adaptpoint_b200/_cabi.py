@@ -56,6 +56,10 @@ _SIGNATURES = {
     "apb_spectral_norm_bwd_f32": [_p, _p, _p, _p, _p, _p, _p, _i, _i, _p],
     "apb_bn_fold_f32": [_p, _p, _p, _p, _f, _p, _p, _p, _i, _p],
     "apb_sums_split_f32": [_p, _p, _p, _i, _p],
+    "apb_bn_finalize_f32": [_p, _d, _f, _f, _p, _p, _p, _p, _p, _p, _p, _p, _i, _p],
+    "apb_sa2_fwd_tf32": [_p] * 7 + [_i, _p, _p, _p, _p, _p] + [_i] * 7 + [_p],
+    "apb_sa2_bwd_rows_tf32": [_p] * 7 + [_i, _p, _p, _p, _i, _i] + [_p] * 9 + [_i] * 6 + [_p],
+    "apb_sa2_wgrad_tf32": [_p] * 7 + [_i, _p, _p, _p, _i] + [_i] * 6 + [_p],
     "apb_bnmax_finalize_f32": [_p, _d, _f, _f, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _p, _p, _p, _i, _i, _i, _p],
     "apb_bnmax_bwd_reduce_f32": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _p],
     "apb_bnmax_bwd_coef_f32": [_p, _p, _p, _p, _p, _d, _p, _p, _p, _p, _i, _p],

@@ -769,6 +769,31 @@ __global__ void bn_fold_kernel(const float *__restrict__ gamma, const float *__r
     shift[c] = beta[c] - mean[c] * s;
 }
 
+// (C,2) sums -> mean, rstd, scale = gamma*rstd, shift = beta - mean*scale, running-statistics update (training-mode BatchNorm
+// whose normalised output is never materialised: the first BatchNorm of the fused two-conv set abstraction, sa_train2.cu)
+__global__ void bn_finalize_kernel(const double *__restrict__ stats, double inv_count, double unbias, float eps,
+                                   float momentum, const float *__restrict__ gamma, const float *__restrict__ beta,
+                                   float *__restrict__ running_mean, float *__restrict__ running_var,
+                                   float *__restrict__ scale, float *__restrict__ shift, float *__restrict__ mean_out,
+                                   float *__restrict__ rstd_out, int C) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const double mean_d = stats[2 * c] * inv_count;
+    double var_d = stats[2 * c + 1] * inv_count - mean_d * mean_d;
+    if (var_d < 0.0) var_d = 0.0;
+    const float mean = (float)mean_d;
+    const float rstd = (float)(1.0 / sqrt(var_d + (double)eps));
+    if (running_mean != nullptr) {
+        running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+        running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)(var_d * unbias);
+    }
+    const float sc = gamma[c] * rstd;
+    scale[c] = sc;
+    shift[c] = beta[c] - mean * sc;
+    mean_out[c] = mean;
+    rstd_out[c] = rstd;
+}
+
 __global__ void sums_split_kernel(const double *__restrict__ sums, float *__restrict__ first, float *__restrict__ second,
                                   int C) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
@@ -783,6 +808,19 @@ extern "C" int apb_bn_fold_f32(const float *gamma, const float *beta, const floa
     if (!gamma || !beta || !running_mean || !running_var || !scale || !shift || !rstd) return APB_E_INVALID;
     bn_fold_kernel<<<apb_div_up(C, 128), 128, 0, (cudaStream_t)stream>>>(gamma, beta, running_mean, running_var, eps, scale,
                                                                          shift, rstd, C);
+    APB_CHECK_LAUNCH();
+    return APB_OK;
+}
+
+extern "C" int apb_bn_finalize_f32(const double *stats, double count, float eps, float momentum, const float *gamma,
+                                   const float *beta, float *running_mean, float *running_var, float *scale, float *shift,
+                                   float *mean, float *rstd, int C, apb_stream_t stream) {
+    if (C <= 0 || count <= 0) return APB_E_INVALID;
+    if (!stats || !gamma || !beta || !scale || !shift || !mean || !rstd || ((running_mean == nullptr) != (running_var == nullptr)))
+        return APB_E_INVALID;
+    bn_finalize_kernel<<<apb_div_up(C, 128), 128, 0, (cudaStream_t)stream>>>(
+        stats, 1.0 / count, count > 1 ? count / (count - 1) : 1.0, eps, momentum, gamma, beta, running_mean, running_var, scale,
+        shift, mean, rstd, C);
     APB_CHECK_LAUNCH();
     return APB_OK;
 }

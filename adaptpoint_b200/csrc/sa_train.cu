@@ -34,7 +34,8 @@ namespace {
 constexpr int GY_QB = 32;      // queries per CTA
 constexpr int GY_CC = 128;     // channels per pass (4 per lane)
 
-// vmax/vmin (B, C, M), arg (B, C, M) = kmax | kmin << 16, stats (C, 2) f64 += sum y, sum y^2 (nullptr: skip)
+// vmax/vmin (B, C, M), arg (B, C, M) = kmax | kmin << 16 (all three nullptr: statistics only), stats (C, 2) f64 += sum y,
+// sum y^2 (nullptr: skip)
 __global__ void __launch_bounds__(256) group_ystats_kernel(const float *__restrict__ U, const float *__restrict__ xyz,
                                                            const float *__restrict__ new_xyz,
                                                            const int32_t *__restrict__ idx, const float *__restrict__ Wp,
@@ -94,7 +95,7 @@ __global__ void __launch_bounds__(256) group_ystats_kernel(const float *__restri
                     }
                 }
             }
-            if (cok) {
+            if (cok && vmax != nullptr) {
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
                     st_max[lane * 4 + e][qi] = mx[e];
@@ -112,7 +113,7 @@ __global__ void __launch_bounds__(256) group_ystats_kernel(const float *__restri
         }
         __syncthreads();
         const int cc = min(GY_CC, C - cbase);
-        for (int i = threadIdx.x; i < cc * GY_QB; i += 256) {
+        for (int i = threadIdx.x; vmax != nullptr && i < cc * GY_QB; i += 256) {
             const int c = i / GY_QB, qi = i - c * GY_QB;
             if (qi < nq) {
                 const size_t o = ((size_t)b * C + cbase + c) * M + m0 + qi;
@@ -285,7 +286,8 @@ extern "C" int apb_group_ystats_f32(const float *u_pm, const float *xyz, const f
                                     int N, int M, int K, int C, apb_stream_t stream) {
     if (B < 0 || N <= 0 || M < 0 || K <= 0 || C <= 0) return APB_E_INVALID;
     if (B == 0 || M == 0) return APB_OK;
-    if (!u_pm || !xyz || !new_xyz || !idx || !wp || !vmax || !vmin || !arg) return APB_E_INVALID;
+    if (!u_pm || !xyz || !new_xyz || !idx || !wp) return APB_E_INVALID;
+    if ((!vmax || !vmin || !arg) && (vmax || vmin || arg || !stats)) return APB_E_INVALID;   // statistics-only pass: all three NULL
     if ((C & 3) != 0 || K > 65535 || B > 65535 || (reinterpret_cast<uintptr_t>(u_pm) & 15) != 0) return APB_E_UNSUPPORTED;
     const size_t smem = (size_t)3 * GY_CC * (GY_QB + 1) * 4 + (size_t)GY_CC * 2 * 8;
     APB_CUDA(cudaFuncSetAttribute((const void *)group_ystats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

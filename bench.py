@@ -104,6 +104,17 @@ def alg_bytes(name, a):
     if name == "apb_sa1_bwd_dense_f32":
         B, N, C = a
         return 4.0 * B * N * (3 * C + 4)
+    # two-conv fused set abstraction (csrc/sa_train2.cu): compulsory HBM bytes -- U once (the gathers hit L2), idx, the
+    # per-query inputs / outputs; nothing of size B*C*M*K exists
+    if name == "apb_sa2_fwd_tf32":
+        _relu, B, N, M, K, C1, C2, _kp = a
+        return 4.0 * B * (N * C1 + M * K + 3 * C2 * M + 3 * N + 3 * M)
+    if name == "apb_sa2_bwd_rows_tf32":
+        _relu, _kp, _kc, B, N, M, K, C1, C2 = a
+        return 4.0 * B * (3 * N * C1 + M * K + 1.25 * M * C2 + 3 * N + 3 * M)
+    if name == "apb_sa2_wgrad_tf32":
+        _relu, _gram, B, N, M, K, C1, C2 = a
+        return 4.0 * B * (N * C1 + M * K + 1.25 * M * C2 + 3 * N + 3 * M)
     if name == "apb_pwconv_wgrad_ld_tf32":
         _ldw, B, Cin, Cout, P = a
         return 4.0 * B * P * (Cin + Cout)

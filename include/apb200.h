@@ -246,6 +246,12 @@ int apb_spectral_norm_bwd_f32(const float *grad, const float *w_sn, const float 
 int apb_bn_fold_f32(const float *gamma, const float *beta, const float *running_mean, const float *running_var, float eps,
                     float *scale, float *shift, float *rstd, int C, apb_stream_t stream);
 int apb_sums_split_f32(const double *sums, float *first, float *second, int C, apb_stream_t stream);
+/* Training-mode BatchNorm whose normalised tensor is never written: (C,2) f64 sums over `count` elements -> mean, rstd,
+ * scale = gamma*rstd, shift = beta - mean*scale, and the running-statistics update (NULL, NULL: skip)
+ * (torch.nn.BatchNorm2d forward in training mode, openpoints/models/layers/norm.py:57-71). */
+int apb_bn_finalize_f32(const double *stats, double count, float eps, float momentum, const float *gamma, const float *beta,
+                        float *running_mean, float *running_var, float *scale, float *shift, float *mean, float *rstd, int C,
+                        apb_stream_t stream);
 
 /* The per-channel arithmetic around BatchNorm -> max over K, in three kernels instead of ~40 element-wise launches:
  *   apb_bnmax_finalize_f32  : (stats (C,2) f64 over `count` elements | NULL = running statistics) -> mean, rstd,
@@ -272,7 +278,7 @@ int apb_bnmax_bwd_coef_f32(const double *tot, const double *local, const float *
  * u_pm (B,N,C) = Wf . f per support point, point-major (apb_pwconv_ex_tf32 with point_major = 1); wp (C,3) = xyz part of
  * the conv weight (already divided by the radius when normalize_dp);  y[b,m,k,c] = u_pm[b,idx,c] + wp[c,:].(p[idx]-q[m]).
  *   apb_group_ystats_f32 : vmax/vmin (B,C,M) = max/min over k of y, arg (B,C,M) = kmax | kmin << 16, stats (C,2) f64 +=
- *                          sum y, sum y^2 (NULL: skip).  C % 4 == 0.
+ *                          sum y, sum y^2 (NULL: skip).  vmax = vmin = arg = NULL: statistics only.  C % 4 == 0.
  *   apb_sa1_bwd_count_f32: cnt (B,N) f32 += occurrences of n in idx[b]; sdp (B,N,3) += sum of (p[n]-q[m]) over them;
  *                          mom (12) f64 += [sum dp (3), sum dp dp^T (9)].  All pre-zeroed by the caller.
  *   apb_sa1_bwd_sparse_f32: for every (b,c,m): du_cm[b,c,idx[b,m,ksel]] += gs; dwp[c,:] += gs*dp (f64, NULL: skip);
@@ -289,6 +295,34 @@ int apb_sa1_bwd_sparse_f32(const float *gs, const int32_t *ksel, const int32_t *
                            int N, int M, int K, int C, apb_stream_t stream);
 int apb_sa1_bwd_dense_f32(const float *u_pm, const float *cnt, const float *sdp, const float *a, const float *bc,
                           const float *wp, float *du_cm, double *usdp, int B, int N, int C, apb_stream_t stream);
+
+/* Training-mode set abstraction for TWO-conv blocks (PointNeXt-S SetAbstraction, sa_layers = 2) without the (B,C,M,K)
+ * tensors, forward and backward (csrc/sa_train2.cu, tcgen05 / TMEM / TMA; replaces QueryAndGroup -> cat -> Conv2d ->
+ * BatchNorm2d -> ReLU -> Conv2d -> BatchNorm2d [-> ReLU] -> max over K of pointnext.py:164-166, layers/conv.py:24-60).
+ * K == 32, C1 % 4 == 0, C2 % 4 == 0, C1, C2 <= 512 (wgrad: C1 <= 256).  u_pm, wp as above; (s1, t1) (C1) = scale / shift of
+ * BatchNorm 1;  h1[r,:] = relu1(s1*(u_pm[idx_r,:] + wp.dp_r) + t1),  y2[r,:] = W2 . h1[r,:].
+ *   apb_sa2_fwd_tf32     : w2 (C2, K2p) fp32, K2p = C1 rounded up to 32, zero padded.  vmax/vmin (B,C2,M) = max/min over k
+ *                          of y2, arg = kmax | kmin << 16, stats (C2,2) f64 += sum y2, sum y2^2 (NULL: skip).
+ *   apb_sa2_bwd_rows_tf32: gs_pm (B*M, C2) f32 = gradient reaching the selected y2 value, ksel_pm (B*M, C2) u8 = its k;
+ *                          wb (C1, Kp) = [ W2^T | G ], W2^T zero-padded to kc_sparse*32 columns, G = W2^T diag(b2) W2 (C1,C1)
+ *                          zero-padded to C1 rounded up to 32 (eval mode: Kp = kc_sparse*32, no G block, vvec = NULL);
+ *                          vvec (C1) = W2^T a2.  dz1 = (wb . [onehot(gs) | h1] + vvec) * [z1 > 0];  du_pm (B,N,C1) pre-zeroed
+ *                          += s1*dz1 at idx;  sums1 (C1,2) f64 += sum dz1, sum dz1*(y1-mean1)*rstd1;  sdzdp (C1,3) f64 +=
+ *                          sum dz1*dp;  sh1 (C1) f64 += sum h1  (sums1 NULL: none of the three);  dxyz (B,N,3) += s1*dz1 . wp,
+ *                          dq (B,M,3) -= the same (NULL: no coordinate gradient).
+ *   apb_sa2_wgrad_tf32   : d_out (C2 [+ C1], C1 rounded up to 32) f32 pre-zeroed: rows [0,C2) += sum_r onehot(gs)[r]^T h1[r],
+ *                          with_gram: rows [C2, C2+C1) += sum_r h1[r] h1[r]^T. */
+int apb_sa2_fwd_tf32(const float *u_pm, const float *xyz, const float *new_xyz, const int32_t *idx, const float *wp,
+                     const float *s1, const float *t1, int relu1, const float *w2, float *vmax, float *vmin, int32_t *arg,
+                     double *stats, int B, int N, int M, int K, int C1, int C2, int K2p, apb_stream_t stream);
+int apb_sa2_bwd_rows_tf32(const float *u_pm, const float *xyz, const float *new_xyz, const int32_t *idx, const float *wp,
+                          const float *s1, const float *t1, int relu1, const float *gs_pm, const uint8_t *ksel_pm,
+                          const float *wb, int Kp, int kc_sparse, const float *vvec, const float *mean1, const float *rstd1,
+                          float *du_pm, double *sums1, double *sdzdp, double *sh1, float *dxyz, float *dq, int B, int N,
+                          int M, int K, int C1, int C2, apb_stream_t stream);
+int apb_sa2_wgrad_tf32(const float *u_pm, const float *xyz, const float *new_xyz, const int32_t *idx, const float *wp,
+                       const float *s1, const float *t1, int relu1, const float *gs_pm, const uint8_t *ksel_pm, float *d_out,
+                       int with_gram, int B, int N, int M, int K, int C1, int C2, apb_stream_t stream);
 
 /* Multi-head self-attention of the imitator (generator_component4_15.py:434-480, Anchor_selfattention.forward:
  * attn = softmax(q k^T / sqrt(d)); out = attn v), head_dim = 16 only (APB_E_UNSUPPORTED otherwise), fp32, scores never
