@@ -101,14 +101,18 @@ def test_model_grads_tc_norm_vs_torch(cuda_dev):
         torch.manual_seed(7)
         if mode == "tcnorm":
             # tc backend for the norm kernels, convs forced back to cuDNN fp32 so only the norm path differs
-            orig = tcconv._use_tc
+            # (the fused set-abstraction path runs its own TF32 GEMMs: off, it has its own tests)
+            from adaptpoint_b200 import fused_train
+            orig, orig_fused = tcconv._use_tc, fused_train.ENABLED
             tcconv._use_tc = lambda m, t: False
+            fused_train.ENABLED = False
             try:
                 with tcconv.conv_backend("tc"):
                     logits, loss = model.get_logits_loss({"pos": xyz, "x": x}, y)
                     loss.backward()
             finally:
                 tcconv._use_tc = orig
+                fused_train.ENABLED = orig_fused
         else:
             logits, loss = model.get_logits_loss({"pos": xyz, "x": x}, y)
             loss.backward()
