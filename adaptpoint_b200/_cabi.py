@@ -27,6 +27,7 @@ _SIGNATURES = {
     "apb_gather_grad_f32": [_p, _p, _p, _i, _i, _i, _i, _p],
     "apb_ball_query_f32": [_p, _p, _p, _i, _i, _i, _f, _i, _p],
     "apb_ball_query_grid_f32": [_p, _p, _p, _p, _ll, _i, _i, _i, _f, _i, _p],
+    "apb_ball_query_grid_static_f32": [_p, _p, _p, _i, _i, _i, _f, _i, _p],
     "apb_knn_f32": [_p, _p, _p, _p, _i, _i, _i, _i, _p],
     "apb_group_f32": [_p, _p, _p, _i, _i, _i, _i, _i, _p],
     "apb_group_bf16": [_p, _p, _p, _i, _i, _i, _i, _i, _p],
@@ -79,7 +80,7 @@ _SIGNATURES = {
                               _i, _i, _i, _i, _i, _i, _i, _i, _i, _p],
 }
 EXPORTED_SYMBOLS = sorted(list(_SIGNATURES) + ["apb_version", "apb_error_string", "apb_fps_block_size",
-                                                  "apb_peer_ws_bytes", "apb_peer_max_elems", "apb_ball_query_grid_ws_bytes", "apb_tune_wgrad"])
+                                                  "apb_peer_ws_bytes", "apb_peer_max_elems", "apb_ball_query_grid_ws_bytes", "apb_ball_query_grid_static_ws_bytes", "apb_tune_wgrad"])
 
 
 class ApbError(RuntimeError):
@@ -112,6 +113,8 @@ def load():
     lib.apb_fps_block_size.argtypes = [_i]
     lib.apb_ball_query_grid_ws_bytes.restype = _ll
     lib.apb_ball_query_grid_ws_bytes.argtypes = [_i, _i]
+    lib.apb_ball_query_grid_static_ws_bytes.restype = _ll
+    lib.apb_ball_query_grid_static_ws_bytes.argtypes = []
     for name in ("apb_peer_ws_bytes", "apb_peer_max_elems"):
         getattr(lib, name).restype = _i
         getattr(lib, name).argtypes = []

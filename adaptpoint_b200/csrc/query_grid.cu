@@ -257,3 +257,42 @@ extern "C" int apb_ball_query_grid_f32(const float *new_xyz, const float *xyz, i
     APB_CHECK_LAUNCH();
     return APB_OK;
 }
+
+// ---- the same query for callers that may not allocate (no counterpart in
+// ---- the reference) ------------------------------------------------------------------------------------------------
+// The cell-grid workspace lives in a file-scope device array instead of caller memory: nothing here (or below it) calls
+// cudaMalloc / cudaFree or any allocating library routine, so the entry point can be used under CUDA graph capture, in
+// serving loops and in harnesses that forbid allocation.  Every GPU that loads libapb200.so holds the array until exit.
+// All calls on a device share it: it keeps the last call's contents (the build kernels re-initialise every field they
+// read, as for caller workspaces with arbitrary contents), and two calls that overlap on the GPU (different streams
+// without an ordering between them) RACE on it.
+#define APB_BQ_STATIC_WS_BYTES (16ll << 20)
+static __device__ __align__(256) unsigned char g_bq_static_ws[APB_BQ_STATIC_WS_BYTES];
+
+namespace {
+constexpr int BQ_MAX_DEVICES = 64;
+void *g_bq_static_ptr[BQ_MAX_DEVICES];   // device address of g_bq_static_ws per device, resolved on first use
+}  // namespace
+
+extern "C" long long apb_ball_query_grid_static_ws_bytes(void) { return APB_BQ_STATIC_WS_BYTES; }
+
+extern "C" int apb_ball_query_grid_static_f32(const float *new_xyz, const float *xyz, int32_t *idx, int B, int N, int M,
+                                              float radius, int nsample, apb_stream_t stream) {
+    if (B < 0 || N < 0 || M < 0 || nsample <= 0) return APB_E_INVALID;
+    if (B == 0 || M == 0) return APB_OK;
+    const long long need = apb_ball_query_grid_ws_bytes(B, N);
+    if (need < 0) return APB_E_INVALID;
+    if (need > APB_BQ_STATIC_WS_BYTES) return APB_E_SCRATCH_LIMIT;
+    int dev = -1;
+    APB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= BQ_MAX_DEVICES) return APB_E_UNSUPPORTED;
+    // In host code `g_bq_static_ws` is only a stand-in for the symbol: its device address on the CURRENT device comes
+    // from the runtime (once per device; a benign race between host threads stores the same value twice).
+    void *ws = __atomic_load_n(&g_bq_static_ptr[dev], __ATOMIC_ACQUIRE);
+    if (ws == nullptr) {
+        APB_CUDA(cudaGetSymbolAddress(&ws, g_bq_static_ws));
+        if (ws == nullptr) return APB_E_INVALID;
+        __atomic_store_n(&g_bq_static_ptr[dev], ws, __ATOMIC_RELEASE);
+    }
+    return apb_ball_query_grid_f32(new_xyz, xyz, idx, ws, APB_BQ_STATIC_WS_BYTES, B, N, M, radius, nsample, stream);
+}

@@ -30,6 +30,7 @@ typedef void *apb_stream_t; /* a cudaStream_t */
 #define APB_OK 0
 #define APB_E_INVALID 10001     /* bad argument (null pointer, negative size, unsupported shape) */
 #define APB_E_UNSUPPORTED 10002 /* shape outside what the kernel family covers */
+#define APB_E_SCRATCH_LIMIT 10003 /* problem needs more than the library's built-in scratch array (no-allocation entry points) */
 
 /* Library / build identification: "apb200 <version> sm_100a". */
 const char *apb_version(void);
@@ -82,6 +83,17 @@ int apb_ball_query_f32(const float *new_xyz, const float *xyz, int32_t *idx, int
 long long apb_ball_query_grid_ws_bytes(int B, int N);
 int apb_ball_query_grid_f32(const float *new_xyz, const float *xyz, int32_t *idx, void *workspace, long long ws_bytes,
                             int B, int N, int M, float radius, int nsample, apb_stream_t stream);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).  apb_ball_query_grid_f32 with
+ * the workspace in a 16 MiB array built into the library (file-scope __device__ array in csrc/query_grid.cu, held by every
+ * GPU that loads the library until exit; apb_ball_query_grid_static_ws_bytes() returns its size): allocates nothing, takes
+ * only inputs and outputs, same results bit for bit.  Returns APB_E_SCRATCH_LIMIT when apb_ball_query_grid_ws_bytes(B, N)
+ * exceeds the array (about B * (262 KB + 20 N bytes): e.g. B = 8, N = 24000 or B = 32, N = 8192 fit).  The device current
+ * at the call must be the one that owns the buffers and the stream.  All calls on a device share the array: calls that
+ * overlap on the GPU (streams with no ordering between them) race -- serialise them. */
+long long apb_ball_query_grid_static_ws_bytes(void);
+int apb_ball_query_grid_static_f32(const float *new_xyz, const float *xyz, int32_t *idx, int B, int N, int M,
+                                   float radius, int nsample, apb_stream_t stream);
 
 /* kNN over squared distances, order (distance, index) ascending.  Replaces KNN.forward =
  * torch.cdist + topk in group.py:12-28 (no native function in the reference).
