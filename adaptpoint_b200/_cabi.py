@@ -21,6 +21,7 @@ _SIGNATURES = {
     "apb_fps_f32": [_p, _p, _p, _i, _i, _i, _p],
     "apb_tune_group": [_i, _i],
     "apb_tune_wgrad": [_i, _i],
+    "apb_tune_sa2": [_i],
     "apb_tune_group_grad": [_i],
     "apb_tune_group_seg": [_i],
     "apb_gather_f32": [_p, _p, _p, _i, _i, _i, _i, _p],

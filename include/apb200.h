@@ -311,7 +311,7 @@ int apb_sa1_bwd_dense_f32(const float *u_pm, const float *cnt, const float *sdp,
 /* Training-mode set abstraction for TWO-conv blocks (PointNeXt-S SetAbstraction, sa_layers = 2) without the (B,C,M,K)
  * tensors, forward and backward (csrc/sa_train2.cu, tcgen05 / TMEM / TMA; replaces QueryAndGroup -> cat -> Conv2d ->
  * BatchNorm2d -> ReLU -> Conv2d -> BatchNorm2d [-> ReLU] -> max over K of pointnext.py:164-166, layers/conv.py:24-60).
- * K == 32, C1 % 4 == 0, C2 % 4 == 0, C1, C2 <= 512 (wgrad: C1 <= 256).  u_pm, wp as above; (s1, t1) (C1) = scale / shift of
+ * K == 32, C1 % 4 == 0, C2 % 4 == 0, C1, C2 <= 512 (backward rows pass and wgrad: C1 <= 256).  u_pm, wp as above; (s1, t1) (C1) = scale / shift of
  * BatchNorm 1;  h1[r,:] = relu1(s1*(u_pm[idx_r,:] + wp.dp_r) + t1),  y2[r,:] = W2 . h1[r,:].
  *   apb_sa2_fwd_tf32     : w2 (C2, K2p) fp32, K2p = C1 rounded up to 32, zero padded.  vmax/vmin (B,C2,M) = max/min over k
  *                          of y2, arg = kmax | kmin << 16, stats (C2,2) f64 += sum y2, sum y2^2 (NULL: skip).
@@ -324,6 +324,7 @@ int apb_sa1_bwd_dense_f32(const float *u_pm, const float *cnt, const float *sdp,
  *                          dq (B,M,3) -= the same (NULL: no coordinate gradient).
  *   apb_sa2_wgrad_tf32   : d_out (C2 [+ C1], C1 rounded up to 32) f32 pre-zeroed: rows [0,C2) += sum_r onehot(gs)[r]^T h1[r],
  *                          with_gram: rows [C2, C2+C1) += sum_r h1[r] h1[r]^T. */
+int apb_tune_sa2(int flags); /* benchmarks only: 1 / 2 / 4 switch off the dU REDs / epilogue U loads / channel sums of the backward rows kernel */
 int apb_sa2_fwd_tf32(const float *u_pm, const float *xyz, const float *new_xyz, const int32_t *idx, const float *wp,
                      const float *s1, const float *t1, int relu1, const float *w2, float *vmax, float *vmin, int32_t *arg,
                      double *stats, int B, int N, int M, int K, int C1, int C2, int K2p, apb_stream_t stream);

@@ -153,8 +153,9 @@ def _sa2_inputs(dev, B, N, M, C1, C2, seed):
     return g, p, q, idx, u, wp, s1, t1, w2
 
 
+# the last three give every CTA several row tiles (pipeline stages and TMEM accumulators are reused many times)
 SA2_SHAPES = [(3, 256, 5, 32, 64), (4, 512, 128, 64, 128), (2, 256, 64, 256, 512), (2, 128, 33, 20, 36),
-              (2, 256, 64, 128, 256)]
+              (2, 256, 64, 128, 256), (8, 1024, 512, 128, 256), (16, 1024, 512, 32, 64), (8, 512, 256, 256, 512)]
 
 
 @pytest.mark.parametrize("B,N,M,C1,C2", SA2_SHAPES)
