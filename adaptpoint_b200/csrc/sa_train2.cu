@@ -276,8 +276,8 @@ sa2_fwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
             nx_dx = nx_dy = nx_dz = 0.f;
             const long long grow = tile * BM + pt;
             if (tile < ntiles && grow < p.rows) {
-                const long long q = grow / p.K;  // b*M + m
-                const long long b = q / p.M;
+                const long long q = grow >> 5;  // b*M + m (K == 32)
+                const long long b = (int)q / p.M;
                 const int n = __ldg(p.idx + grow);
                 const float *pp = p.xyz + (b * p.N + n) * 3;
                 const float *qq = p.new_xyz + q * 3;
@@ -367,8 +367,8 @@ sa2_fwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
                         if (y < mn) { mn = y; kn = j; }
                     }
                     if (qvalid && cvalid) {
-                        const long long q = row0 / p.K;
-                        const long long b = q / p.M, m = q - b * p.M;
+                        const long long q = row0 >> 5;
+                        const long long b = (int)q / p.M, m = q - b * p.M;
                         const size_t o = ((size_t)b * p.C2 + c) * p.M + m;
                         p.vmax[o] = mx;
                         p.vmin[o] = mn;
@@ -515,8 +515,8 @@ sa2_bwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
             nx_dx = nx_dy = nx_dz = 0.f;
             const long long grow = tile * BM + pt;
             if (tile < ntiles && grow < p.rows) {
-                const long long q = grow / p.K;  // b*M + m
-                const long long b = q / p.M;
+                const long long q = grow >> 5;  // b*M + m (K == 32)
+                const long long b = (int)q / p.M;
                 const int n = __ldg(p.idx + grow);
                 const float *pp = p.xyz + (b * p.N + n) * 3;
                 const float *qq = p.new_xyz + q * 3;
@@ -549,10 +549,9 @@ sa2_bwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
                     const int d0 = kc * 32 + l8 * 4;
 #pragma unroll
                     for (int step = 0; step < 8; ++step) {
-                        const long long grow = tile * BM + pw * 32 + step * 4 + lr;
-                        const long long q = grow / p.K;
+                        // K == 32: the 32 rows pw*32.. of the tile are the neighbours k = 0..31 of query tile*4 + pw
                         v[step] = (ur[step] >= 0 && d0 < p.C2)
-                                      ? onehot_quad(p.gs_pm, p.ksel_pm, q, p.C2, d0, (int)(grow - q * p.K))
+                                      ? onehot_quad(p.gs_pm, p.ksel_pm, tile * 4 + pw, p.C2, d0, step * 4 + lr)
                                       : make_float4(0.f, 0.f, 0.f, 0.f);
                     }
                     tc::mbar_wait(&empty_bar[s], ph ^ 1);
@@ -594,8 +593,8 @@ sa2_bwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
             const uint32_t aph = (lt >> 1) & 1;
             const long long row0 = tile * BM + q4 * 32;      // the 32 rows of this warp: the K neighbours of ONE query
             const bool qvalid = row0 < p.rows;
-            const long long q = row0 / p.K;
-            const long long b = q / p.M;
+            const long long q = row0 >> 5;
+            const long long b = (int)q / p.M;
             long long urow = 0;
             float dx = 0.f, dy = 0.f, dz = 0.f;
             if (qvalid) {   // row metadata, loaded before the accumulator wait
@@ -852,26 +851,23 @@ __global__ void __launch_bounds__(WG_THREADS, 1) sa2_wgrad_kernel(const W2Params
             const int s = my_stage;
             const uint32_t ph = (it / p.stages) & 1;
             const long long row0 = chunk_row0(it);
-            long long qrow[8];
-            int urow[8], krow[8];
+            // K == 32: the 32 rows of a chunk are the neighbours k = 0..31 of ONE query
+            const long long q = row0 >> 5;
+            const long long bq = (int)q / p.M;
+            const float *qq = p.new_xyz + (row0 < p.rows ? q : 0) * 3;   // (chunks past the last row of the last tile)
+            const float qx = __ldg(qq + 0), qy = __ldg(qq + 1), qz = __ldg(qq + 2);
+            int urow[8];
             float dx[8], dy[8], dz[8];
 #pragma unroll
             for (int step = 0; step < 8; ++step) {
-                const long long grow = row0 + step * 4 + lr;
                 urow[step] = -1;
-                qrow[step] = 0; krow[step] = 0;
                 dx[step] = dy[step] = dz[step] = 0.f;
                 if (nidx[step] >= 0) {
-                    const long long q = grow / p.K;
-                    const long long b = q / p.M;
-                    urow[step] = (int)(b * p.N + nidx[step]);
-                    qrow[step] = q;
-                    krow[step] = (int)(grow - q * p.K);
+                    urow[step] = (int)(bq * p.N + nidx[step]);
                     const float *pp = p.xyz + (size_t)urow[step] * 3;
-                    const float *qq = p.new_xyz + q * 3;
-                    dx[step] = __ldg(pp + 0) - __ldg(qq + 0);
-                    dy[step] = __ldg(pp + 1) - __ldg(qq + 1);
-                    dz[step] = __ldg(pp + 2) - __ldg(qq + 2);
+                    dx[step] = __ldg(pp + 0) - qx;
+                    dy[step] = __ldg(pp + 1) - qy;
+                    dz[step] = __ldg(pp + 2) - qz;
                 }
             }
             fetch_idx(it + p.stages);
@@ -885,7 +881,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) sa2_wgrad_kernel(const W2Params
                 if (ch < p.C2) {
 #pragma unroll
                     for (int step = 0; step < 8; ++step)
-                        v[step] = urow[step] >= 0 ? onehot_quad(p.gs_pm, p.ksel_pm, qrow[step], p.C2, ch, krow[step])
+                        v[step] = urow[step] >= 0 ? onehot_quad(p.gs_pm, p.ksel_pm, q, p.C2, ch, step * 4 + lr)
                                                   : make_float4(0.f, 0.f, 0.f, 0.f);
                 } else {
                     const int c = ch - p.C2;
@@ -1036,7 +1032,7 @@ int g_sa2_dbg = 0;
 
 bool s2_shapes_ok(int B, int N, int M, int K, int C1, int C2) {
     return B > 0 && N > 0 && M > 0 && K == 32 && C1 > 0 && C2 > 0 && (C1 & 3) == 0 && (C2 & 3) == 0 && C1 <= 512 &&
-           C2 <= 512 && (long long)B * N < (1ll << 31);
+           C2 <= 512 && (long long)B * N < (1ll << 31) && (long long)B * M < (1ll << 31);
 }
 
 }  // namespace
