@@ -547,14 +547,21 @@ sa2_bwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
                 float4 v[8];
                 if (kc < p.kc_sparse) {
                     const int d0 = kc * 32 + l8 * 4;
+                    // K == 32: the 32 rows pw*32.. of the tile are the neighbours k = 0..31 of query tile*4 + pw: one load of
+                    // that query's gs / ksel quad, 8 one-hot variants
+                    const bool ok = ur[0] >= 0 && d0 < p.C2;
+                    const long long qoff = (tile * 4 + pw) * p.C2 + d0;
+                    const float4 g = ok ? __ldg(reinterpret_cast<const float4 *>(p.gs_pm + qoff)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    const uint32_t kq = ok ? __ldg(reinterpret_cast<const uint32_t *>(p.ksel_pm + qoff)) : 0xffffffffu;
+                    tc::mbar_wait(&empty_bar[s], ph ^ 1);
 #pragma unroll
                     for (int step = 0; step < 8; ++step) {
-                        // K == 32: the 32 rows pw*32.. of the tile are the neighbours k = 0..31 of query tile*4 + pw
-                        v[step] = (ur[step] >= 0 && d0 < p.C2)
-                                      ? onehot_quad(p.gs_pm, p.ksel_pm, tile * 4 + pw, p.C2, d0, step * 4 + lr)
-                                      : make_float4(0.f, 0.f, 0.f, 0.f);
+                        const int k = step * 4 + lr;
+                        v[step].x = (int)(kq & 0xff) == k ? g.x : 0.f;
+                        v[step].y = (int)((kq >> 8) & 0xff) == k ? g.y : 0.f;
+                        v[step].z = (int)((kq >> 16) & 0xff) == k ? g.z : 0.f;
+                        v[step].w = (int)(kq >> 24) == k ? g.w : 0.f;
                     }
-                    tc::mbar_wait(&empty_bar[s], ph ^ 1);
                 } else {
                     const int c0 = (kc - p.kc_sparse) * 32 + l8 * 4;
                     const bool cvalid = c0 < p.C1;   // C1 % 4 == 0: a lane's 4 channels are all valid or all padding
@@ -879,10 +886,18 @@ __global__ void __launch_bounds__(WG_THREADS, 1) sa2_wgrad_kernel(const W2Params
                 const int ch = bx < nboxA ? (slab0 * 4 + bx) * 32 + l8 * 4 : p.C2 + (bx - nboxA) * 32 + l8 * 4;
                 float4 v[8];
                 if (ch < p.C2) {
+                    // the chunk's 32 rows share one query: one load of its gs / ksel quad, 8 one-hot variants
+                    const bool ok = row0 < p.rows;
+                    const float4 g = ok ? __ldg(reinterpret_cast<const float4 *>(p.gs_pm + q * p.C2 + ch)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    const uint32_t kq = ok ? __ldg(reinterpret_cast<const uint32_t *>(p.ksel_pm + q * p.C2 + ch)) : 0xffffffffu;
 #pragma unroll
-                    for (int step = 0; step < 8; ++step)
-                        v[step] = urow[step] >= 0 ? onehot_quad(p.gs_pm, p.ksel_pm, q, p.C2, ch, step * 4 + lr)
-                                                  : make_float4(0.f, 0.f, 0.f, 0.f);
+                    for (int step = 0; step < 8; ++step) {
+                        const int k = step * 4 + lr;
+                        v[step].x = (int)(kq & 0xff) == k ? g.x : 0.f;
+                        v[step].y = (int)((kq >> 8) & 0xff) == k ? g.y : 0.f;
+                        v[step].z = (int)((kq >> 16) & 0xff) == k ? g.z : 0.f;
+                        v[step].w = (int)(kq >> 24) == k ? g.w : 0.f;
+                    }
                 } else {
                     const int c = ch - p.C2;
                     const bool cvalid = c < p.C1 && (bx >= nboxA || ch < p.Mtot);
