@@ -188,8 +188,10 @@ class SaTwoLayerFn(Function):
             _cabi.call("apb_pwconv_ex_tf32", [fs, wb, None, None, 0, u, 1, None, None, B, cin, C1, N, kp], dev)
         s1, t1, mean1, rstd1 = (torch.empty(C1, dtype=torch.float32, device=dev) for _ in range(4))
         n1 = 1.0
+        stats1 = stats2 = None
         if training:   # pass 1: batch statistics of the first conv's output
-            stats1 = torch.zeros((C1, 2), dtype=torch.float64, device=dev)
+            st = torch.zeros((C1 + C2, 2), dtype=torch.float64, device=dev)     # one fill for both statistics
+            stats1, stats2 = st[:C1], st[C1:]
             _cabi.call("apb_group_ystats_f32", [u, ps, qs, idx, wp, None, None, None, stats1, B, N, M, K, C1], dev)
             n1 = float(B * M * K * norm._allreduce(stats1, group))
             _cabi.call("apb_bn_finalize_f32", [stats1, n1, float(eps1), float(mom1 or 0.0), g1.detach(), b1.detach(), rm1,
@@ -201,7 +203,6 @@ class SaTwoLayerFn(Function):
         vmax = torch.empty((B, C2, M), dtype=torch.float32, device=dev)
         vmin = torch.empty_like(vmax)
         arg = torch.empty((B, C2, M), dtype=torch.int32, device=dev)
-        stats2 = torch.zeros((C2, 2), dtype=torch.float64, device=dev) if training else None
         _cabi.call("apb_sa2_fwd_tf32", [u, ps, qs, idx, wp, s1, t1, 1, w2b, vmax, vmin, arg, stats2, B, N, M, K, C1, C2,
                                         k2p], dev)
         n2 = 1.0
@@ -209,7 +210,7 @@ class SaTwoLayerFn(Function):
             n2 = float(B * M * K * norm._allreduce(stats2, group))
         out, sel, ksel, scale2, mean2, rstd2 = norm.bnmax_post(vmax, vmin, arg, stats2, n2, g2, b2, rm2, rv2, mom2, eps2,
                                                                relu2, training)
-        ksel_pm = ksel.transpose(1, 2).to(torch.uint8).contiguous()      # (B, M, C2)
+        ksel_pm = torch.empty((B, M, C2), dtype=torch.uint8, device=dev).copy_(ksel.transpose(1, 2))   # one kernel
         ctx.save_for_backward(ps, qs, fs, idx, u, sel, ksel_pm, out if relu2 else None, scale2, mean2, rstd2, wp, wf, W2, s1,
                               t1, mean1, rstd1)
         ctx.cfg = (relu2, training, group, n1, n2, inv_r, tuple(w1.shape), tuple(w2.shape))
@@ -230,24 +231,32 @@ class SaTwoLayerFn(Function):
         need_w = ctx.needs_input_grad[4] or ctx.needs_input_grad[11]
         need_bn1 = ctx.needs_input_grad[5] or ctx.needs_input_grad[6]
         kc2, c1pad = (C2 + 31) // 32, (C1 + 31) // 32 * 32
-        wb = torch.zeros((C1, kc2 * 32 + (c1pad if training else 0)), dtype=torch.float32, device=dev)
-        wb[:, :C2] = W2.t()
-        vvec = None
-        if training:   # dense BatchNorm-2 terms: dh1 += W2^T a2 + (W2^T diag(b2) W2) h1
-            wb[:, kc2 * 32:kc2 * 32 + C1] = W2.t() @ (b2c.view(C2, 1) * W2)
-            vvec = (W2.t() @ a2).contiguous()
-        du_pm = torch.zeros((B, N, C1), dtype=torch.float32, device=dev)
         want_sums = training or need_w or need_bn1
-        sums1 = torch.zeros((C1, 2), dtype=torch.float64, device=dev) if want_sums else None
-        sdzdp = torch.zeros((C1, 3), dtype=torch.float64, device=dev) if want_sums else None
-        sh1 = torch.zeros(C1, dtype=torch.float64, device=dev) if want_sums else None
+        # one fp32 and one fp64 zero fill for everything the kernels accumulate into
+        kw = kc2 * 32 + (c1pad if training else 0)
+        n_du, n_wb, n_dm = B * N * C1, C1 * kw, ((C2 + (C1 if training else 0)) * c1pad if need_w else 0)
+        z32 = torch.zeros(n_du + n_wb + n_dm, dtype=torch.float32, device=dev)
+        du_pm = z32[:n_du].view(B, N, C1)
+        wb = z32[n_du:n_du + n_wb].view(C1, kw)
+        dmat = z32[n_du + n_wb:].view(-1, c1pad) if need_w else None
+        sums1 = sdzdp = sh1 = usdp = None
+        if want_sums:
+            z64 = torch.zeros(9 * C1, dtype=torch.float64, device=dev)
+            sums1, sdzdp = z64[:2 * C1].view(C1, 2), z64[2 * C1:5 * C1].view(C1, 3)
+            sh1, usdp = z64[5 * C1:6 * C1], z64[6 * C1:].view(C1, 3)
+        wb[:, :C2] = W2.t()
+        vvec = bw = None
+        if training:   # dense BatchNorm-2 terms: dh1 += W2^T a2 + (W2^T diag(b2) W2) h1
+            bw = b2c.view(C2, 1) * W2
+            wb[:, kc2 * 32:kc2 * 32 + C1] = W2.t() @ bw
+            vvec = (W2.t() @ a2).contiguous()
         dxyz = torch.zeros_like(ps) if ctx.needs_input_grad[0] else None
         dq = torch.zeros_like(qs) if ctx.needs_input_grad[1] else None
         _cabi.call("apb_sa2_bwd_rows_tf32", [u, ps, qs, idx, wp, s1, t1, 1, gs_pm, ksel_pm, wb, wb.shape[1], kc2, vvec, mean1,
                                              rstd1, du_pm, sums1, sdzdp, sh1, dxyz, dq, B, N, M, K, C1, C2], dev)
         du = du_pm.transpose(1, 2).contiguous()                          # (B, C1, N) for the dgrad / wgrad GEMMs
         dgamma1 = dbeta1 = None
-        dwp = s1.double().view(C1, 1) * sdzdp if need_w else None       # sum_r (s1 * dz1) dp
+        dwp = None
         if training:
             tot1 = sums1
             if group is not None and torch.distributed.is_initialized() and torch.distributed.get_world_size(group) > 1:
@@ -257,12 +266,14 @@ class SaTwoLayerFn(Function):
             dgamma1, dbeta1 = (torch.empty(C1, dtype=torch.float32, device=dev) for _ in range(2))
             _cabi.call("apb_bnmax_bwd_coef_f32", [tot1, sums1, s1, mean1, rstd1, float(n1), a1, b1c, dgamma1, dbeta1, C1], dev)
             cnt, sdp, mom = _idx_moments(ps, qs, idx)
-            usdp = torch.zeros((C1, 3), dtype=torch.float64, device=dev)
             _cabi.call("apb_sa1_bwd_dense_f32", [u, cnt, sdp, a1, b1c, wp, du, usdp, B, N, C1], dev)
-            if need_w:
-                m1, m2 = mom[:3], mom[3:].view(3, 3)
-                dwp = dwp + a1.double().view(C1, 1) * m1.view(1, 3) + b1c.double().view(C1, 1) * (usdp + wp.double() @ m2)
-        elif need_bn1:
+            if need_w:   # dWp = s1 * sum dz1 dp + a1 S1^T + b1 * (U^T sdp + Wp S2)
+                cd = torch.stack([s1, a1, b1c, wp[:, 0], wp[:, 1], wp[:, 2]]).double()      # one conversion for all
+                dwp = torch.addmm(usdp, cd[3:].t(), mom[3:].view(3, 3)).mul_(cd[2].view(C1, 1))
+                dwp.addcmul_(cd[0].view(C1, 1), sdzdp).add_(torch.outer(cd[1], mom[:3]))
+        elif need_w:
+            dwp = s1.double().view(C1, 1) * sdzdp                          # sum_r (s1 * dz1) dp
+        if not training and need_bn1:
             dbeta1, dgamma1 = (torch.empty(C1, dtype=torch.float32, device=dev) for _ in range(2))
             _cabi.call("apb_sums_split_f32", [sums1, dbeta1, dgamma1, C1], dev)
         df = dw1 = dw2 = None
@@ -272,12 +283,11 @@ class SaTwoLayerFn(Function):
         if need_w:
             dwf = torch.einsum("bon,bin->oi", du, fs) if EXACT_GEMM else tcconv.wgrad(du, fs, B, cin, C1, N)
             dw1 = torch.cat([(dwp * inv_r).float(), dwf], dim=1).view(w1shape)
-            dmat = torch.zeros((C2 + (C1 if training else 0), c1pad), dtype=torch.float32, device=dev)
             _cabi.call("apb_sa2_wgrad_tf32", [u, ps, qs, idx, wp, s1, t1, 1, gs_pm, ksel_pm, dmat, int(training), B, N, M, K,
                                               C1, C2], dev)
             dw2 = dmat[:C2, :C1]
-            if training:   # dense terms of dy2: a2 (sum h1)^T + diag(b2) W2 (sum h1 h1^T)
-                dw2 = dw2 + a2.view(C2, 1) * sh1.float().view(1, C1) + b2c.view(C2, 1) * (W2 @ dmat[C2:C2 + C1, :C1])
+            if training:   # dense terms of dy2: diag(b2) W2 (sum h1 h1^T) + a2 (sum h1)^T
+                dw2 = torch.addmm(dw2, bw, dmat[C2:C2 + C1, :C1]).addr_(a2, sh1.float())
             dw2 = dw2.reshape(w2shape)
         # BatchNorm parameter gradients are per-rank sums (the data-parallel all-reduce averages them afterwards)
         return (dxyz, dq, df, None, dw1, dgamma1, dbeta1, None, None, None, None, dw2, dgamma2, dbeta2, None, None, None,
