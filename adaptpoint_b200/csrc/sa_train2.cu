@@ -82,7 +82,8 @@ struct S2Params {
     double *sdzdp;         // (C1, 3) += sum dz1 * dp
     double *sh1;           // (C1)    += sum h1
     float *dxyz, *dq;      // (B, N, 3), (B, M, 3) pre-zeroed or nullptr
-    int dbg;               // benchmarks only (apb_tune_sa2): 1 skip the dU REDs, 2 skip the epilogue's U loads, 4 skip the sums
+    int dbg;               // benchmarks only (apb_tune_sa2): 1 skip the dU REDs, 2 the epilogue's U loads, 4 the sums,
+                           // 8 the producers' U loads, 16 their h1 arithmetic, 32 the epilogue's row metadata
 };
 
 __device__ __forceinline__ uint8_t *align1024(uint8_t *p) {
@@ -567,14 +568,14 @@ sa2_bwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
                     const bool cvalid = c0 < p.C1;   // C1 % 4 == 0: a lane's 4 channels are all valid or all padding
 #pragma unroll
                     for (int step = 0; step < 8; ++step)   // rows of U for the 8 steps, issued up front
-                        v[step] = (ur[step] >= 0 && cvalid)
+                        v[step] = (ur[step] >= 0 && cvalid && !(p.dbg & 8))
                                       ? __ldg(reinterpret_cast<const float4 *>(p.U + (size_t)ur[step] * p.C1 + c0))
                                       : make_float4(0.f, 0.f, 0.f, 0.f);
                     tc::mbar_wait(&empty_bar[s], ph ^ 1);
 #pragma unroll
                     for (int step = 0; step < 8; ++step) {
                         const int r = pw * 32 + step * 4 + lr;
-                        if (ur[step] >= 0 && cvalid)
+                        if (ur[step] >= 0 && cvalid && !(p.dbg & 16))
                             v[step] = h1_quad(prm, c1pad, c0, v[step], meta_dp[(mb * 3 + 0) * BM + r],
                                               meta_dp[(mb * 3 + 1) * BM + r], meta_dp[(mb * 3 + 2) * BM + r], p.relu1);
                     }
@@ -604,7 +605,7 @@ sa2_bwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
             const long long b = (int)q / p.M;
             long long urow = 0;
             float dx = 0.f, dy = 0.f, dz = 0.f;
-            if (qvalid) {   // row metadata, loaded before the accumulator wait
+            if (qvalid && !(p.dbg & 32)) {   // row metadata, loaded before the accumulator wait
                 const int n = __ldg(p.idx + row0 + lane);
                 urow = b * p.N + n;
                 const float *pp = p.xyz + urow * 3;

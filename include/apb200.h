@@ -324,7 +324,7 @@ int apb_sa1_bwd_dense_f32(const float *u_pm, const float *cnt, const float *sdp,
  *                          dq (B,M,3) -= the same (NULL: no coordinate gradient).
  *   apb_sa2_wgrad_tf32   : d_out (C2 [+ C1], C1 rounded up to 32) f32 pre-zeroed: rows [0,C2) += sum_r onehot(gs)[r]^T h1[r],
  *                          with_gram: rows [C2, C2+C1) += sum_r h1[r] h1[r]^T. */
-int apb_tune_sa2(int flags); /* benchmarks only: 1 / 2 / 4 switch off the dU REDs / epilogue U loads / channel sums of the backward rows kernel */
+int apb_tune_sa2(int flags); /* benchmarks only (results are then wrong): bits 1 / 2 / 4 / 8 / 16 / 32 switch off the dU REDs / epilogue U loads / channel sums / producer U loads / producer h1 arithmetic / epilogue row metadata of the backward rows kernel */
 int apb_sa2_fwd_tf32(const float *u_pm, const float *xyz, const float *new_xyz, const int32_t *idx, const float *wp,
                      const float *s1, const float *t1, int relu1, const float *w2, float *vmax, float *vmin, int32_t *arg,
                      double *stats, int B, int N, int M, int K, int C1, int C2, int K2p, apb_stream_t stream);
