@@ -47,9 +47,9 @@ constexpr int PROD0 = 64;
 constexpr int EPI0 = PROD0 + 128 * NGROUPS;
 constexpr int NTHREADS = EPI0 + 128;
 constexpr int MAX_STAGES = 6;
-// backward rows kernel: one producer group, two epilogue groups (one per TMEM accumulator stage)
-constexpr int BW_EPI0 = PROD0 + 128;
-constexpr int BW_THREADS = BW_EPI0 + 256;
+// backward rows kernel: two producer groups, two epilogue groups (one per TMEM accumulator stage), 16-channel epilogue blocks
+constexpr int BW_THREADS = PROD0 + 128 * NGROUPS + 256;
+constexpr int EB = 16;
 constexpr int NPRM = 8;            // s1, t1, wx, wy, wz, v, mean1, rstd1
 constexpr int NSUM = 6;            // backward channel sums: dz, dz*xhat, dz*dpx, dz*dpy, dz*dpz, h1
 
@@ -109,6 +109,26 @@ __device__ __forceinline__ float colsum32(float (&x)[32], int lane) {
     colsum_step<2>(x, lane);
     colsum_step<1>(x, lane);
     return x[0];
+}
+
+// 16-column variant: x[j] of lane l = (row l, column j), j < 16.  Returns in every lane l the sum over the 32 rows of
+// column l & 15.
+template <int S>
+__device__ __forceinline__ void colsum16_step(float (&x)[16], int lane) {
+    const bool up = (lane & S) != 0;
+#pragma unroll
+    for (int i = 0; i < S; ++i) {
+        const float send = up ? x[i] : x[i + S];
+        const float keep = up ? x[i + S] : x[i];
+        x[i] = keep + __shfl_xor_sync(0xffffffffu, send, S);
+    }
+}
+__device__ __forceinline__ float colsum16(float (&x)[16], int lane) {
+    colsum16_step<8>(x, lane);
+    colsum16_step<4>(x, lane);
+    colsum16_step<2>(x, lane);
+    colsum16_step<1>(x, lane);
+    return x[0] + __shfl_xor_sync(0xffffffffu, x[0], 16);
 }
 
 __device__ __forceinline__ void red_add_v4(float *dst, float a, float b, float c, float d) {
@@ -403,12 +423,14 @@ sa2_fwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
     }
 }
 
-// ---- sa2_bwd_kernel: persistent, one CTA per SM, 448 threads, warp-specialised ---------------------------------------
+// ---- sa2_bwd_kernel: persistent, one CTA per SM, 576 threads, warp-specialised ---------------------------------------
 //    warp 0       TMA producer for the [W2^T | G] chunk of every pipeline stage (the N operand, C1 rows)
 //    warp 1       TMEM allocator + single-thread tcgen05.mma issuer (UMMA 128 x NCP x 8, tf32 -> fp32)
-//    warps 2-5    row-tile producers (8 lanes per row): one-hot gs chunks, then h1 chunks
-//    warps 6-9    epilogue of the even tiles (TMEM accumulator stage 0), thread <-> row (TMEM lane)
-//    warps 10-13  epilogue of the odd tiles  (TMEM accumulator stage 1)
+//    warps 2-9    row-tile producers (2 groups of 128 threads, alternating tiles, 8 lanes per row): one-hot gs chunks,
+//                 then h1 chunks
+//    warps 10-13  epilogue of the even tiles (TMEM accumulator stage 0), thread <-> row (TMEM lane)
+//    warps 14-17  epilogue of the odd tiles  (TMEM accumulator stage 1)
+// The epilogue works on column blocks of 16 channels so that the whole kernel fits 112 registers per thread.
 // COORDS: also the gradient to the coordinates (dxyz, dq)
 template <bool COORDS>
 __global__ void __launch_bounds__(BW_THREADS, 1)
@@ -425,11 +447,12 @@ sa2_bwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty_bar + 2);
     float *prm = reinterpret_cast<float *>(tail + 256);       // [NPRM][c1pad]
     const int c1pad = p.c1pad;
-    int *meta_row = reinterpret_cast<int *>(prm + NPRM * c1pad);     // producers: [2][BM]
-    float *meta_dp = reinterpret_cast<float *>(meta_row + 2 * BM);   // [2][3][BM]
-    float *wacc = meta_dp + 6 * BM;                                  // [8 epilogue warps][NSUM][c1pad]
+    int *meta_row = reinterpret_cast<int *>(prm + NPRM * c1pad);               // producers: [NGROUPS][2][BM]
+    float *meta_dp = reinterpret_cast<float *>(meta_row + NGROUPS * 2 * BM);   // [NGROUPS][2][3][BM]
+    float *sacc = meta_dp + NGROUPS * 6 * BM;                                  // [NSUM][c1pad] channel sums of the CTA
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t spg = p.stages / NGROUPS;   // smem stages per producer group
     const long long ntiles = (p.rows + BM - 1) / BM;
     const bool want_sums = p.sums1 != nullptr;
 
@@ -457,8 +480,7 @@ sa2_bwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
         prm[6 * c1pad + c] = (ok && p.mean1 != nullptr) ? p.mean1[c] : 0.f;
         prm[7 * c1pad + c] = (ok && p.rstd1 != nullptr) ? p.rstd1[c] : 0.f;
     }
-    if (want_sums)
-        for (int i = tid; i < 8 * NSUM * c1pad; i += BW_THREADS) wacc[i] = 0.f;
+    for (int i = tid; i < NSUM * c1pad; i += BW_THREADS) sacc[i] = 0.f;
     tc::tc_fence_before();
     __syncthreads();
     tc::tc_fence_after();
@@ -467,11 +489,13 @@ sa2_bwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
     if (warp == 0) {
         // ===================== TMA producer =====================
         if (lane == 0) {
-            uint32_t it = 0;
-            for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            uint32_t lt = 0;
+            for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++lt) {
+                const int grp = lt % NGROUPS;
+                uint32_t it = (lt / NGROUPS) * (uint32_t)p.kchunks;   // chunk counter of this group's own stage ring
                 for (int kc = 0; kc < p.kchunks; ++kc, ++it) {
-                    const int s = it % p.stages;
-                    const uint32_t ph = (it / p.stages) & 1;
+                    const int s = grp * spg + it % spg;
+                    const uint32_t ph = (it / spg) & 1;
                     tc::mbar_wait(&empty_bar[s], ph ^ 1);
                     uint8_t *wdst = smem + (size_t)s * stage_bytes + A_BYTES;
                     tc::mbar_arrive_expect_tx(&full_bar[s], (uint32_t)w_bytes);
@@ -483,16 +507,18 @@ sa2_bwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
         // ===================== MMA issuer =====================
         if (lane == 0) {
             const uint32_t idesc = tc::idesc_tf32_f32(BM, p.NCP);
-            uint32_t lt = 0, it = 0;
+            uint32_t lt = 0;
             for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++lt) {
+                const int grp = lt % NGROUPS;
+                uint32_t it = (lt / NGROUPS) * (uint32_t)p.kchunks;
                 const int a = lt & 1;
                 const uint32_t aph = (lt >> 1) & 1;
                 tc::mbar_wait(&tempty_bar[a], aph ^ 1);
                 tc::tc_fence_after();
                 const uint32_t tacc = tmem_base + (uint32_t)a * 256;
                 for (int kc = 0; kc < p.kchunks; ++kc, ++it) {
-                    const int s = it % p.stages;
-                    const uint32_t ph = (it / p.stages) & 1;
+                    const int s = grp * spg + it % spg;
+                    const uint32_t ph = (it / spg) & 1;
                     tc::mbar_wait(&full_bar[s], ph);
                     tc::tc_fence_after();
                     const uint32_t a_addr = tc::smem_u32(smem + (size_t)s * stage_bytes);
@@ -506,9 +532,12 @@ sa2_bwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
                 tc::umma_commit(&tfull_bar[a]);      // accumulator complete -> epilogue
             }
         }
-    } else if (warp < 6) {
-        // ===================== row-tile producers (128 threads, 8 lanes per row, 4 channels per lane) =====================
-        const int pt = tid - PROD0;   // also the row whose metadata this thread fetches
+    } else if (warp < 2 + 4 * NGROUPS) {
+        // ===================== row-tile producers: group g fills tiles lt % NGROUPS == g =====================
+        const int grp = (warp - 2) >> 2;
+        const int pt = (tid - PROD0) & 127;   // also the row whose metadata this thread fetches
+        int *g_meta_row = meta_row + grp * 2 * BM;
+        float *g_meta_dp = meta_dp + grp * 6 * BM;
         int nx_urow = -1;
         float nx_dx = 0.f, nx_dy = 0.f, nx_dz = 0.f;
         auto fetch_meta = [&](long long tile) {
@@ -527,23 +556,25 @@ sa2_bwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
                 nx_urow = (int)(b * p.N + n);
             }
         };
-        fetch_meta(blockIdx.x);
+        fetch_meta((long long)blockIdx.x + (long long)grp * gridDim.x);
         const int pw = pt >> 5, l8 = lane & 7, lr = lane >> 3;
-        uint32_t lt = 0, it = 0;
+        uint32_t lt = 0;
         for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++lt) {
-            const int mb = lt & 1;
-            meta_row[mb * BM + pt] = nx_urow;
-            meta_dp[(mb * 3 + 0) * BM + pt] = nx_dx;
-            meta_dp[(mb * 3 + 1) * BM + pt] = nx_dy;
-            meta_dp[(mb * 3 + 2) * BM + pt] = nx_dz;
-            named_bar_sync(1, 128);
-            fetch_meta(tile + gridDim.x);   // next tile, consumed next round
+            if ((int)(lt % NGROUPS) != grp) continue;
+            uint32_t it = (lt / NGROUPS) * (uint32_t)p.kchunks;   // this group's own stage ring (in-order => parity-safe)
+            const int mb = (lt / NGROUPS) & 1;
+            g_meta_row[mb * BM + pt] = nx_urow;
+            g_meta_dp[(mb * 3 + 0) * BM + pt] = nx_dx;
+            g_meta_dp[(mb * 3 + 1) * BM + pt] = nx_dy;
+            g_meta_dp[(mb * 3 + 2) * BM + pt] = nx_dz;
+            named_bar_sync(1 + grp, 128);
+            fetch_meta(tile + (long long)NGROUPS * gridDim.x);   // next tile of this group, consumed next round
             int ur[8];
 #pragma unroll
-            for (int step = 0; step < 8; ++step) ur[step] = meta_row[mb * BM + pw * 32 + step * 4 + lr];
+            for (int step = 0; step < 8; ++step) ur[step] = g_meta_row[mb * BM + pw * 32 + step * 4 + lr];
             for (int kc = 0; kc < p.kchunks; ++kc, ++it) {
-                const int s = it % p.stages;
-                const uint32_t ph = (it / p.stages) & 1;
+                const int s = grp * spg + it % spg;
+                const uint32_t ph = (it / spg) & 1;
                 const uint32_t abase = tc::smem_u32(smem + (size_t)s * stage_bytes);
                 float4 v[8];
                 if (kc < p.kc_sparse) {
@@ -576,8 +607,8 @@ sa2_bwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
                     for (int step = 0; step < 8; ++step) {
                         const int r = pw * 32 + step * 4 + lr;
                         if (ur[step] >= 0 && cvalid && !(p.dbg & 16))
-                            v[step] = h1_quad(prm, c1pad, c0, v[step], meta_dp[(mb * 3 + 0) * BM + r],
-                                              meta_dp[(mb * 3 + 1) * BM + r], meta_dp[(mb * 3 + 2) * BM + r], p.relu1);
+                            v[step] = h1_quad(prm, c1pad, c0, v[step], g_meta_dp[(mb * 3 + 0) * BM + r],
+                                              g_meta_dp[(mb * 3 + 1) * BM + r], g_meta_dp[(mb * 3 + 2) * BM + r], p.relu1);
                     }
                 }
 #pragma unroll
@@ -592,9 +623,8 @@ sa2_bwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
         }
     } else {
         // ===================== epilogue: group g = accumulator stage g = tiles with lt % 2 == g =====================
-        const int grp = (warp - 6) >> 2;
-        const int q4 = warp & 3;     // TMEM lane quarter of this warp (warps 6..9 -> 2,3,0,1; 10..13 -> 2,3,0,1)
-        float *myacc = wacc + (warp - 6) * NSUM * c1pad;
+        const int grp = (warp - (2 + 4 * NGROUPS)) >> 2;
+        const int q4 = warp & 3;     // TMEM lane quarter of this warp (warps 10..13 -> 2,3,0,1; 14..17 -> 2,3,0,1)
         uint32_t lt = 0;
         for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++lt) {
             if ((int)(lt & 1) != grp) continue;
@@ -618,20 +648,20 @@ sa2_bwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
             tc::tc_fence_after();
             const uint32_t tacc = tmem_base + (uint32_t)grp * 256 + ((uint32_t)(q4 * 32) << 16);
             float gx = 0.f, gy = 0.f, gz = 0.f;
-            for (int cb = 0; cb < p.NCP; cb += 32) {
-                float y1[32], dzv[32];
+            for (int cb = 0; cb < p.NCP; cb += EB) {
+                float y1[EB], dzv[EB];
                 const float *up = p.U + urow * p.C1 + cb;
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {   // this row of U, issued before the TMEM load completes
+                for (int j = 0; j < EB / 4; ++j) {   // this row of U, issued before the TMEM load completes
                     const float4 u = (qvalid && cb + 4 * j < p.C1 && !(p.dbg & 2)) ? __ldg(reinterpret_cast<const float4 *>(up) + j)
-                                                                   : make_float4(0.f, 0.f, 0.f, 0.f);
+                                                                                   : make_float4(0.f, 0.f, 0.f, 0.f);
                     y1[4 * j + 0] = u.x; y1[4 * j + 1] = u.y; y1[4 * j + 2] = u.z; y1[4 * j + 3] = u.w;
                 }
-                uint32_t v[32];
-                tc::tmem_ld_32x32(tacc + cb, v);
+                uint32_t v[EB];
+                tc::tmem_ld_32x16(tacc + cb, v);
                 tc::tmem_ld_wait();
 #pragma unroll
-                for (int j4 = 0; j4 < 32; j4 += 4) {
+                for (int j4 = 0; j4 < EB; j4 += 4) {
                     const int c = cb + j4;   // < c1pad: padding channels carry zero parameters
                     const float4 ps = *reinterpret_cast<const float4 *>(prm + 0 * c1pad + c);
                     const float4 pt1 = *reinterpret_cast<const float4 *>(prm + 1 * c1pad + c);
@@ -661,38 +691,38 @@ sa2_bwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
                     }
                     if (qvalid && c < p.C1 && !(p.dbg & 1)) red_add_v4(p.dU_pm + urow * p.C1 + c, ds[0], ds[1], ds[2], ds[3]);
                 }
-                if (want_sums && !(p.dbg & 4)) {
-                    const int c = cb + lane;
-                    float t[32];
+                if (want_sums && !(p.dbg & 4) && cb < c1pad) {
+                    float t[EB];
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) t[j] = dzv[j];
-                    const float a0 = colsum32(t, lane);
+                    for (int j = 0; j < EB; ++j) t[j] = dzv[j];
+                    const float a0 = colsum16(t, lane);
 #pragma unroll
-                    for (int j = 0; j < 32; ++j)
+                    for (int j = 0; j < EB; ++j)
                         t[j] = dzv[j] * (y1[j] - prm[6 * c1pad + cb + j]) * prm[7 * c1pad + cb + j];
-                    const float a1 = colsum32(t, lane);
+                    const float a1 = colsum16(t, lane);
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) t[j] = dzv[j] * dx;
-                    const float a2 = colsum32(t, lane);
+                    for (int j = 0; j < EB; ++j) t[j] = dzv[j] * dx;
+                    const float a2 = colsum16(t, lane);
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) t[j] = dzv[j] * dy;
-                    const float a3 = colsum32(t, lane);
+                    for (int j = 0; j < EB; ++j) t[j] = dzv[j] * dy;
+                    const float a3 = colsum16(t, lane);
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) t[j] = dzv[j] * dz;
-                    const float a4 = colsum32(t, lane);
+                    for (int j = 0; j < EB; ++j) t[j] = dzv[j] * dz;
+                    const float a4 = colsum16(t, lane);
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) {
+                    for (int j = 0; j < EB; ++j) {
                         const float z = fmaf(prm[0 * c1pad + cb + j], y1[j], prm[1 * c1pad + cb + j]);
                         t[j] = (qvalid && cb + j < p.C1) ? (p.relu1 ? fmaxf(z, 0.f) : z) : 0.f;
                     }
-                    const float a5 = colsum32(t, lane);
-                    if (c < c1pad) {
-                        myacc[0 * c1pad + c] += a0;
-                        myacc[1 * c1pad + c] += a1;
-                        myacc[2 * c1pad + c] += a2;
-                        myacc[3 * c1pad + c] += a3;
-                        myacc[4 * c1pad + c] += a4;
-                        myacc[5 * c1pad + c] += a5;
+                    const float a5 = colsum16(t, lane);
+                    if (lane < EB) {   // lane l holds the sums of channel cb + l
+                        const int c = cb + lane;
+                        atomicAdd(sacc + 0 * c1pad + c, a0);
+                        atomicAdd(sacc + 1 * c1pad + c, a1);
+                        atomicAdd(sacc + 2 * c1pad + c, a2);
+                        atomicAdd(sacc + 3 * c1pad + c, a3);
+                        atomicAdd(sacc + 4 * c1pad + c, a4);
+                        atomicAdd(sacc + 5 * c1pad + c, a5);
                     }
                 }
             }
@@ -717,16 +747,17 @@ sa2_bwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
                 }
             }
         }
-        if (want_sums) {   // flush this warp's channel sums
-            for (int c = lane; c < p.C1; c += 32) {
-                atomicAdd(p.sums1 + 2 * c, (double)myacc[0 * c1pad + c]);
-                atomicAdd(p.sums1 + 2 * c + 1, (double)myacc[1 * c1pad + c]);
+        if (want_sums) {   // all epilogue warps done -> flush the CTA's channel sums
+            named_bar_sync(3, 256);
+            for (int c = tid - (PROD0 + 128 * NGROUPS); c < p.C1; c += 256) {
+                atomicAdd(p.sums1 + 2 * c, (double)sacc[0 * c1pad + c]);
+                atomicAdd(p.sums1 + 2 * c + 1, (double)sacc[1 * c1pad + c]);
                 if (p.sdzdp != nullptr) {
-                    atomicAdd(p.sdzdp + 3 * c + 0, (double)myacc[2 * c1pad + c]);
-                    atomicAdd(p.sdzdp + 3 * c + 1, (double)myacc[3 * c1pad + c]);
-                    atomicAdd(p.sdzdp + 3 * c + 2, (double)myacc[4 * c1pad + c]);
+                    atomicAdd(p.sdzdp + 3 * c + 0, (double)sacc[2 * c1pad + c]);
+                    atomicAdd(p.sdzdp + 3 * c + 1, (double)sacc[3 * c1pad + c]);
+                    atomicAdd(p.sdzdp + 3 * c + 2, (double)sacc[4 * c1pad + c]);
                 }
-                if (p.sh1 != nullptr) atomicAdd(p.sh1 + c, (double)myacc[5 * c1pad + c]);
+                if (p.sh1 != nullptr) atomicAdd(p.sh1 + c, (double)sacc[5 * c1pad + c]);
             }
         }
     }
@@ -1025,11 +1056,12 @@ int launch_bwd(S2Params p, const float *W, int Kp, cudaStream_t st) {
     p.NCP = (p.C1 + 15) / 16 * 16;
     if (p.NCP > 256) return APB_E_UNSUPPORTED;   // two accumulator stages of <= 256 columns
     const int stage_bytes = A_BYTES + p.NCP * 128;
-    const size_t extra = 1024 /*align slack*/ + 256 /*barriers*/ + (size_t)NPRM * p.c1pad * 4 + (size_t)8 * BM * 4 /*metadata*/ +
-                         (p.sums1 != nullptr ? (size_t)8 * NSUM * p.c1pad * 4 : 0);
+    const size_t extra = 1024 /*align slack*/ + 256 /*barriers*/ + (size_t)NPRM * p.c1pad * 4 +
+                         (size_t)NGROUPS * 8 * BM * 4 /*metadata*/ + (size_t)NSUM * p.c1pad * 4 /*channel sums*/;
     int stages = (int)((227 * 1024 - extra) / stage_bytes);
     if (stages > MAX_STAGES) stages = MAX_STAGES;
-    if (stages < 2) return APB_E_UNSUPPORTED;
+    stages = stages / NGROUPS * NGROUPS;   // each producer group owns its own in-order ring
+    if (stages < NGROUPS) return APB_E_UNSUPPORTED;
     p.stages = stages;
     size_t smem = (size_t)stages * stage_bytes + extra;
     if (smem < 120 * 1024) smem = 120 * 1024;   // one CTA per SM: every CTA allocates all 512 TMEM columns
