@@ -69,6 +69,7 @@ _SIGNATURES = {
     "apb_sa1_bwd_count_f32": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
     "apb_sa1_bwd_sparse_f32": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p],
     "apb_sa1_bwd_dense_f32": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _p],
+    "apb_sa_ustats_f32": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _p],
     "apb_attn_small_fwd_f32": [_p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
     "apb_attn_small_bwd_f32": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
     "apb_rowmax_f32": [_p, _p, _p, _ll, _i, _p],

@@ -338,3 +338,74 @@ extern "C" int apb_sa1_bwd_dense_f32(const float *u_pm, const float *cnt, const 
     APB_CHECK_LAUNCH();
     return APB_OK;
 }
+
+// ---- batch statistics of y[r, c] = U[n_r, c] + Wp[c, :] . dp_r WITHOUT a pass over the rows r ------------------------------
+// With cnt[n] / sdp[n] / S1 / S2 of apb_sa1_bwd_count_f32 (they depend on idx only):
+//   sum_r y    = sum_n cnt[n] U[n, c]                                  + Wp[c, :] . S1
+//   sum_r y^2  = sum_n (cnt[n] U[n, c]^2 + 2 U[n, c] Wp[c, :] . sdp[n]) + Wp[c, :] S2 Wp[c, :]^T
+// one pass over the B*N*C values of U instead of B*M*K*C gathered ones (16x fewer for a stride-2 block with K = 32).
+namespace {
+
+__global__ void __launch_bounds__(256) sa_ustats_kernel(const float *__restrict__ U, const float *__restrict__ cnt,
+                                                        const float *__restrict__ sdp, const float *__restrict__ Wp,
+                                                        const double *__restrict__ mom, double *__restrict__ stats, int N,
+                                                        int C) {
+    __shared__ float red[2][8][32];
+    __shared__ float s_cnt[32], s_sdp[32][3];
+    const int b = blockIdx.z, n0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    if (threadIdx.x < 32) {
+        const int n = n0 + threadIdx.x;
+        s_cnt[threadIdx.x] = n < N ? cnt[(size_t)b * N + n] : 0.f;
+#pragma unroll
+        for (int j = 0; j < 3; ++j) s_sdp[threadIdx.x][j] = n < N ? sdp[((size_t)b * N + n) * 3 + j] : 0.f;
+    }
+    __syncthreads();
+    const int c = c0 + tx;
+    const bool cok = c < C;
+    const float w0 = cok ? Wp[c * 3] : 0.f, w1 = cok ? Wp[c * 3 + 1] : 0.f, w2 = cok ? Wp[c * 3 + 2] : 0.f;
+    float a = 0.f, q = 0.f;
+    for (int r = ty; r < 32; r += 8) {
+        const int n = n0 + r;
+        if (n < N && cok) {
+            const float u = __ldg(U + ((size_t)b * N + n) * C + c);
+            const float cn = s_cnt[r];
+            const float ws = fmaf(w0, s_sdp[r][0], fmaf(w1, s_sdp[r][1], w2 * s_sdp[r][2]));
+            a = fmaf(cn, u, a);
+            q = fmaf(u, fmaf(cn, u, 2.f * ws), q);
+        }
+    }
+    red[0][ty][tx] = a;
+    red[1][ty][tx] = q;
+    __syncthreads();
+    if (threadIdx.x < 64) {
+        const int k = threadIdx.x >> 5, t = threadIdx.x & 31;
+        double v = 0.0;
+        for (int g = 0; g < 8; ++g) v += (double)red[k][g][t];
+        const int cc = c0 + t;
+        if (cc < C) {
+            if (blockIdx.x == 0 && b == 0) {   // the terms that do not depend on U, once per channel
+                const double x0 = Wp[cc * 3], x1 = Wp[cc * 3 + 1], x2 = Wp[cc * 3 + 2];
+                if (k == 0) v += x0 * mom[0] + x1 * mom[1] + x2 * mom[2];
+                else
+                    v += x0 * (x0 * mom[3] + x1 * mom[4] + x2 * mom[5]) + x1 * (x0 * mom[6] + x1 * mom[7] + x2 * mom[8]) +
+                         x2 * (x0 * mom[9] + x1 * mom[10] + x2 * mom[11]);
+            }
+            atomicAdd(stats + 2 * (size_t)cc + k, v);
+        }
+    }
+}
+
+}  // namespace
+
+extern "C" int apb_sa_ustats_f32(const float *u_pm, const float *cnt, const float *sdp, const float *wp, const double *mom,
+                                 double *stats, int B, int N, int C, apb_stream_t stream) {
+    if (B < 0 || N <= 0 || C <= 0) return APB_E_INVALID;
+    if (B == 0) return APB_OK;
+    if (!u_pm || !cnt || !sdp || !wp || !mom || !stats) return APB_E_INVALID;
+    if (B > 65535 || apb_div_up(C, 32) > 65535) return APB_E_UNSUPPORTED;
+    sa_ustats_kernel<<<dim3(apb_div_up(N, 32), apb_div_up(C, 32), B), 256, 0, (cudaStream_t)stream>>>(u_pm, cnt, sdp, wp, mom,
+                                                                                                       stats, N, C);
+    APB_CHECK_LAUNCH();
+    return APB_OK;
+}

@@ -192,7 +192,10 @@ class SaTwoLayerFn(Function):
         if training:   # pass 1: batch statistics of the first conv's output
             st = torch.zeros((C1 + C2, 2), dtype=torch.float64, device=dev)     # one fill for both statistics
             stats1, stats2 = st[:C1], st[C1:]
-            _cabi.call("apb_group_ystats_f32", [u, ps, qs, idx, wp, None, None, None, stats1, B, N, M, K, C1], dev)
+            # closed form from the idx-only moments (cnt, sdp, S1, S2; cached per step, the backward pass needs them too):
+            # one pass over the B*N*C1 values of U instead of the B*M*K*C1 gathered ones
+            cnt, sdp, mom = _idx_moments(ps, qs, idx)
+            _cabi.call("apb_sa_ustats_f32", [u, cnt, sdp, wp, mom, stats1, B, N, C1], dev)
             n1 = float(B * M * K * norm._allreduce(stats1, group))
             _cabi.call("apb_bn_finalize_f32", [stats1, n1, float(eps1), float(mom1 or 0.0), g1.detach(), b1.detach(), rm1,
                                                rv1, s1, t1, mean1, rstd1, C1], dev)

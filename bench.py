@@ -104,6 +104,9 @@ def alg_bytes(name, a):
     if name == "apb_sa1_bwd_dense_f32":
         B, N, C = a
         return 4.0 * B * N * (3 * C + 4)
+    if name == "apb_sa_ustats_f32":
+        B, N, C = a
+        return 4.0 * B * N * (C + 4)
     # two-conv fused set abstraction (csrc/sa_train2.cu): compulsory HBM bytes -- U once (the gathers hit L2), idx, the
     # per-query inputs / outputs; nothing of size B*C*M*K exists
     if name == "apb_sa2_fwd_tf32":

@@ -307,6 +307,11 @@ int apb_sa1_bwd_sparse_f32(const float *gs, const int32_t *ksel, const int32_t *
                            int N, int M, int K, int C, apb_stream_t stream);
 int apb_sa1_bwd_dense_f32(const float *u_pm, const float *cnt, const float *sdp, const float *a, const float *bc,
                           const float *wp, float *du_cm, double *usdp, int B, int N, int C, apb_stream_t stream);
+/* Batch statistics of y (sum y, sum y^2 per channel, added to stats (C,2) f64) in closed form from cnt / sdp / mom of
+ * apb_sa1_bwd_count_f32: one pass over the B*N*C values of u_pm instead of the B*M*K*C gathered ones (the statistics
+ * of the first BatchNorm2d of a two-conv block, openpoints/models/layers/conv.py:24-60 in training mode). */
+int apb_sa_ustats_f32(const float *u_pm, const float *cnt, const float *sdp, const float *wp, const double *mom,
+                      double *stats, int B, int N, int C, apb_stream_t stream);
 
 /* Training-mode set abstraction for TWO-conv blocks (PointNeXt-S SetAbstraction, sa_layers = 2) without the (B,C,M,K)
  * tensors, forward and backward (csrc/sa_train2.cu, tcgen05 / TMEM / TMA; replaces QueryAndGroup -> cat -> Conv2d ->

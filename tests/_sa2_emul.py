@@ -182,6 +182,13 @@ def apb_sa1_bwd_dense_f32(u, cnt, sdp, a, bc, wp, du_cm, usdp, B, N, C):
     usdp += torch.einsum("bnc,bnj->cj", ud, sd)
 
 
+def apb_sa_ustats_f32(u, cnt, sdp, wp, mom, stats, B, N, C):
+    ud, cn, sd, w = u.double(), cnt.double().unsqueeze(-1), sdp.double(), wp.double()
+    ws = sd @ w.t()                                            # (B,N,C): Wp[c,:] . sdp[n]
+    stats[:, 0] += (cn * ud).sum(dim=(0, 1)) + w @ mom[:3]
+    stats[:, 1] += (cn * ud * ud + 2 * ud * ws).sum(dim=(0, 1)) + ((w @ mom[3:].view(3, 3)) * w).sum(dim=1)
+
+
 def apb_sums_split_f32(sums, first, second, C):
     first.copy_(sums[:, 0])
     second.copy_(sums[:, 1])

@@ -295,3 +295,31 @@ def test_set_abstraction_two_layer_fused_train_vs_unfused(cuda_dev, cin, cout, B
     assert "apb_sa2_fwd_tf32" in launched and "apb_sa2_bwd_rows_tf32" in launched and "apb_sa2_wgrad_tf32" in launched
     assert "apb_group_f32" not in launched, "the grouped tensor must not be built"
     _compare_tf32_two(got, want, not training)
+
+
+@pytest.mark.parametrize("B,N,M,C1", [(3, 256, 5, 32), (4, 512, 128, 64), (2, 130, 33, 20), (8, 1024, 512, 128)])
+def test_sa_ustats_closed_form_equals_gathered_statistics(cuda_dev, B, N, M, C1):
+    """apb_sa_ustats_f32 (sum y, sum y^2 from cnt / sdp / moments, one pass over U) against apb_group_ystats_f32 (the same
+    sums taken over the B*M*K gathered rows) and the float64 restatement."""
+    import _sa2_emul as emul
+    from adaptpoint_b200 import _cabi
+    _, p, q, idx, u, wp, _, _, _ = _sa2_inputs(cuda_dev, B, N, M, C1, 8, C1 + N)
+    K = 32
+    cnt = torch.zeros((B, N), device=cuda_dev)
+    sdp = torch.zeros((B, N, 3), device=cuda_dev)
+    mom = torch.zeros(12, dtype=torch.float64, device=cuda_dev)
+    _cabi.call("apb_sa1_bwd_count_f32", [p, q, idx, cnt, sdp, mom, B, N, M, K], cuda_dev)
+    got = torch.zeros((C1, 2), dtype=torch.float64, device=cuda_dev)
+    _cabi.call("apb_sa_ustats_f32", [u, cnt, sdp, wp, mom, got, B, N, C1], cuda_dev)
+    direct = torch.zeros((C1, 2), dtype=torch.float64, device=cuda_dev)
+    _cabi.call("apb_group_ystats_f32", [u, p, q, idx, wp, None, None, None, direct, B, N, M, K, C1], cuda_dev)
+    want = torch.zeros((C1, 2), dtype=torch.float64, device=cuda_dev)
+    emul.apb_group_ystats_f32(u, p, q, idx, wp, None, None, None, want, B, N, M, K, C1)
+    torch.cuda.synchronize()
+    n = B * M * K
+    # mean and variance, the quantities BatchNorm uses
+    for name, s in (("closed form", got), ("gathered", direct)):
+        mean, ex2 = s[:, 0] / n, s[:, 1] / n
+        wmean, wex2 = want[:, 0] / n, want[:, 1] / n
+        assert (mean - wmean).abs().max().item() < 1e-5 * (1 + wmean.abs().max().item()), name
+        assert ((ex2 - mean * mean) - (wex2 - wmean * wmean)).abs().max().item() < 1e-4 * (wex2 - wmean * wmean).max().item(), name
