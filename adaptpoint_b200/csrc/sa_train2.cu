@@ -12,7 +12,7 @@
 //   h1 = relu(s1 * y1 + t1)                   (s1, t1) = BatchNorm 1 (batch or running statistics)
 //   y2 = W2 . h1                              B*M*K rows on the tensor cores
 //   out = act(BN2(max_k y2 or min_k y2))      BatchNorm + ReLU are monotone per channel (norm.cu, bnmax_finalize)
-// forward, pass 1 (sa_train.cu group_ystats_kernel, statistics only): sum y1, sum y1^2 -> (s1, t1).
+// forward, pass 1 (sa_train.cu sa_ustats_kernel): sum y1, sum y1^2 in closed form from U and the idx-only moments -> (s1, t1).
 // forward, pass 2 (sa2_fwd_kernel): producer warps gather rows of U (8 lanes per row, coalesced), form h1 in registers and
 //   store it as a TF32 tile (128 rows x 32 channels per stage, 128B swizzle); W2 chunks arrive by TMA.  The GEMM is issued
 //   TRANSPOSED -- D^T[channel, row] = W2 . h1^T, weights as the M = 128 operand, the row tile as N = 128 -- so that in
