@@ -138,11 +138,11 @@ __device__ __forceinline__ void red_add_v4(float *dst, float a, float b, float c
 // h1 of 4 consecutive channels of one row: relu(s1 * (u + Wp . dp) + t1); prm = [NPRM][c1pad] in shared memory
 __device__ __forceinline__ float4 h1_quad(const float *prm, int c1pad, int c, float4 u, float dx, float dy, float dz,
                                           int relu1) {
-    const float4 s = *reinterpret_cast<const float4 *>(prm + 0 * c1pad + c);
-    const float4 t = *reinterpret_cast<const float4 *>(prm + 1 * c1pad + c);
-    const float4 wx = *reinterpret_cast<const float4 *>(prm + 2 * c1pad + c);
-    const float4 wy = *reinterpret_cast<const float4 *>(prm + 3 * c1pad + c);
-    const float4 wz = *reinterpret_cast<const float4 *>(prm + 4 * c1pad + c);
+    const float4 s = tc::lds_f4_ro(prm + 0 * c1pad + c);
+    const float4 t = tc::lds_f4_ro(prm + 1 * c1pad + c);
+    const float4 wx = tc::lds_f4_ro(prm + 2 * c1pad + c);
+    const float4 wy = tc::lds_f4_ro(prm + 3 * c1pad + c);
+    const float4 wz = tc::lds_f4_ro(prm + 4 * c1pad + c);
     float4 h;
     h.x = fmaf(s.x, fmaf(wz.x, dz, fmaf(wy.x, dy, fmaf(wx.x, dx, u.x))), t.x);
     h.y = fmaf(s.y, fmaf(wz.y, dz, fmaf(wy.y, dy, fmaf(wx.y, dx, u.y))), t.y);
@@ -322,7 +322,7 @@ sa2_fwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
             fetch_meta(tile + (long long)NGROUPS * gridDim.x);  // next tile of this group, consumed next round
             int ur[8];
 #pragma unroll
-            for (int step = 0; step < 8; ++step) ur[step] = g_meta_row[mb * BM + pw * 32 + step * 4 + lr];
+            for (int step = 0; step < 8; ++step) ur[step] = tc::lds_i(g_meta_row + mb * BM + pw * 32 + step * 4 + lr);
             for (int kc = 0; kc < p.kchunks; ++kc, ++it) {
                 const int s = grp * spg + it % spg;
                 const uint32_t ph = (it / spg) & 1;
@@ -340,8 +340,8 @@ sa2_fwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
                 for (int step = 0; step < 8; ++step) {
                     const int r = pw * 32 + step * 4 + lr;
                     if (ur[step] >= 0 && cvalid)
-                        v[step] = h1_quad(prm, c1pad, c0, v[step], g_meta_dp[(mb * 3 + 0) * BM + r],
-                                          g_meta_dp[(mb * 3 + 1) * BM + r], g_meta_dp[(mb * 3 + 2) * BM + r], p.relu1);
+                        v[step] = h1_quad(prm, c1pad, c0, v[step], tc::lds_f(g_meta_dp + (mb * 3 + 0) * BM + r),
+                                          tc::lds_f(g_meta_dp + (mb * 3 + 1) * BM + r), tc::lds_f(g_meta_dp + (mb * 3 + 2) * BM + r), p.relu1);
                     tc::st_shared_v4(abase + r * 128 + ((l8 ^ (r & 7)) << 4), tc::to_tf32(v[step].x), tc::to_tf32(v[step].y),
                                      tc::to_tf32(v[step].z), tc::to_tf32(v[step].w));
                 }
@@ -571,7 +571,7 @@ sa2_bwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
             fetch_meta(tile + (long long)NGROUPS * gridDim.x);   // next tile of this group, consumed next round
             int ur[8];
 #pragma unroll
-            for (int step = 0; step < 8; ++step) ur[step] = g_meta_row[mb * BM + pw * 32 + step * 4 + lr];
+            for (int step = 0; step < 8; ++step) ur[step] = tc::lds_i(g_meta_row + mb * BM + pw * 32 + step * 4 + lr);
             for (int kc = 0; kc < p.kchunks; ++kc, ++it) {
                 const int s = grp * spg + it % spg;
                 const uint32_t ph = (it / spg) & 1;
@@ -607,8 +607,9 @@ sa2_bwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
                     for (int step = 0; step < 8; ++step) {
                         const int r = pw * 32 + step * 4 + lr;
                         if (ur[step] >= 0 && cvalid && !(p.dbg & 16))
-                            v[step] = h1_quad(prm, c1pad, c0, v[step], g_meta_dp[(mb * 3 + 0) * BM + r],
-                                              g_meta_dp[(mb * 3 + 1) * BM + r], g_meta_dp[(mb * 3 + 2) * BM + r], p.relu1);
+                            v[step] = h1_quad(prm, c1pad, c0, v[step], tc::lds_f(g_meta_dp + (mb * 3 + 0) * BM + r),
+                                              tc::lds_f(g_meta_dp + (mb * 3 + 1) * BM + r), tc::lds_f(g_meta_dp + (mb * 3 + 2) * BM + r),
+                                              p.relu1);
                     }
                 }
 #pragma unroll
@@ -663,12 +664,12 @@ sa2_bwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
 #pragma unroll
                 for (int j4 = 0; j4 < EB; j4 += 4) {
                     const int c = cb + j4;   // < c1pad: padding channels carry zero parameters
-                    const float4 ps = *reinterpret_cast<const float4 *>(prm + 0 * c1pad + c);
-                    const float4 pt1 = *reinterpret_cast<const float4 *>(prm + 1 * c1pad + c);
-                    const float4 pwx = *reinterpret_cast<const float4 *>(prm + 2 * c1pad + c);
-                    const float4 pwy = *reinterpret_cast<const float4 *>(prm + 3 * c1pad + c);
-                    const float4 pwz = *reinterpret_cast<const float4 *>(prm + 4 * c1pad + c);
-                    const float4 pvv = *reinterpret_cast<const float4 *>(prm + 5 * c1pad + c);
+                    const float4 ps = tc::lds_f4_ro(prm + 0 * c1pad + c);
+                    const float4 pt1 = tc::lds_f4_ro(prm + 1 * c1pad + c);
+                    const float4 pwx = tc::lds_f4_ro(prm + 2 * c1pad + c);
+                    const float4 pwy = tc::lds_f4_ro(prm + 3 * c1pad + c);
+                    const float4 pwz = tc::lds_f4_ro(prm + 4 * c1pad + c);
+                    const float4 pvv = tc::lds_f4_ro(prm + 5 * c1pad + c);
                     const float s_[4] = {ps.x, ps.y, ps.z, ps.w}, t_[4] = {pt1.x, pt1.y, pt1.z, pt1.w};
                     const float wx_[4] = {pwx.x, pwx.y, pwx.z, pwx.w}, wy_[4] = {pwy.x, pwy.y, pwy.z, pwy.w};
                     const float wz_[4] = {pwz.x, pwz.y, pwz.z, pwz.w}, vv_[4] = {pvv.x, pvv.y, pvv.z, pvv.w};
@@ -698,7 +699,7 @@ sa2_bwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
                     const float a0 = colsum16(t, lane);
 #pragma unroll
                     for (int j = 0; j < EB; ++j)
-                        t[j] = dzv[j] * (y1[j] - prm[6 * c1pad + cb + j]) * prm[7 * c1pad + cb + j];
+                        t[j] = dzv[j] * (y1[j] - tc::lds_f_ro(prm + 6 * c1pad + cb + j)) * tc::lds_f_ro(prm + 7 * c1pad + cb + j);
                     const float a1 = colsum16(t, lane);
 #pragma unroll
                     for (int j = 0; j < EB; ++j) t[j] = dzv[j] * dx;
@@ -711,7 +712,7 @@ sa2_bwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
                     const float a4 = colsum16(t, lane);
 #pragma unroll
                     for (int j = 0; j < EB; ++j) {
-                        const float z = fmaf(prm[0 * c1pad + cb + j], y1[j], prm[1 * c1pad + cb + j]);
+                        const float z = fmaf(tc::lds_f_ro(prm + 0 * c1pad + cb + j), y1[j], tc::lds_f_ro(prm + 1 * c1pad + cb + j));
                         t[j] = (qvalid && cb + j < p.C1) ? (p.relu1 ? fmaxf(z, 0.f) : z) : 0.f;
                     }
                     const float a5 = colsum16(t, lane);

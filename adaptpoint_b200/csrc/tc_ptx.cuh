@@ -176,6 +176,30 @@ __device__ __forceinline__ uint32_t to_tf32(float f) {  // round-to-nearest tf32
 __device__ __forceinline__ void st_shared_v4(uint32_t saddr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(saddr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
+// Shared-memory loads with an explicit state space: pointers derived from the aligned dynamic-smem base through integer
+// casts lose it, and the compiler then emits generic LD.E (longer latency than LDS).
+// *_ro: data that is constant after the kernel's prologue (the compiler may move / merge these loads);
+// the others are ordered like volatile accesses (buffers rewritten between barriers).
+__device__ __forceinline__ float4 lds_f4_ro(const float *p) {
+    float4 r;
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(smem_u32(p)));
+    return r;
+}
+__device__ __forceinline__ float lds_f_ro(const float *p) {
+    float r;
+    asm("ld.shared.f32 %0, [%1];" : "=f"(r) : "r"(smem_u32(p)));
+    return r;
+}
+__device__ __forceinline__ float lds_f(const float *p) {
+    float r;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(r) : "r"(smem_u32(p)) : "memory");
+    return r;
+}
+__device__ __forceinline__ int lds_i(const int *p) {
+    int r;
+    asm volatile("ld.shared.s32 %0, [%1];" : "=r"(r) : "r"(smem_u32(p)) : "memory");
+    return r;
+}
 __device__ __forceinline__ bool elect_one() {
     uint32_t pred;
     asm volatile(
