@@ -314,10 +314,10 @@ sa2_fwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
             if ((int)(lt % NGROUPS) != grp) continue;
             uint32_t it = (lt / NGROUPS) * (uint32_t)p.kchunks;  // this group's own stage ring (in-order => parity-safe)
             const int mb = (lt / NGROUPS) & 1;
-            g_meta_row[mb * BM + pt] = nx_urow;
-            g_meta_dp[(mb * 3 + 0) * BM + pt] = nx_dx;
-            g_meta_dp[(mb * 3 + 1) * BM + pt] = nx_dy;
-            g_meta_dp[(mb * 3 + 2) * BM + pt] = nx_dz;
+            tc::sts_i(g_meta_row + mb * BM + pt, nx_urow);
+            tc::sts_f(g_meta_dp + (mb * 3 + 0) * BM + pt, nx_dx);
+            tc::sts_f(g_meta_dp + (mb * 3 + 1) * BM + pt, nx_dy);
+            tc::sts_f(g_meta_dp + (mb * 3 + 2) * BM + pt, nx_dz);
             named_bar_sync(1 + grp, 128);
             fetch_meta(tile + (long long)NGROUPS * gridDim.x);  // next tile of this group, consumed next round
             int ur[8];
@@ -563,10 +563,10 @@ sa2_bwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
             if ((int)(lt % NGROUPS) != grp) continue;
             uint32_t it = (lt / NGROUPS) * (uint32_t)p.kchunks;   // this group's own stage ring (in-order => parity-safe)
             const int mb = (lt / NGROUPS) & 1;
-            g_meta_row[mb * BM + pt] = nx_urow;
-            g_meta_dp[(mb * 3 + 0) * BM + pt] = nx_dx;
-            g_meta_dp[(mb * 3 + 1) * BM + pt] = nx_dy;
-            g_meta_dp[(mb * 3 + 2) * BM + pt] = nx_dz;
+            tc::sts_i(g_meta_row + mb * BM + pt, nx_urow);
+            tc::sts_f(g_meta_dp + (mb * 3 + 0) * BM + pt, nx_dx);
+            tc::sts_f(g_meta_dp + (mb * 3 + 1) * BM + pt, nx_dy);
+            tc::sts_f(g_meta_dp + (mb * 3 + 2) * BM + pt, nx_dz);
             named_bar_sync(1 + grp, 128);
             fetch_meta(tile + (long long)NGROUPS * gridDim.x);   // next tile of this group, consumed next round
             int ur[8];
@@ -718,12 +718,12 @@ sa2_bwd_kernel(const __grid_constant__ CUtensorMap wmap, const S2Params p) {
                     const float a5 = colsum16(t, lane);
                     if (lane < EB) {   // lane l holds the sums of channel cb + l
                         const int c = cb + lane;
-                        atomicAdd(sacc + 0 * c1pad + c, a0);
-                        atomicAdd(sacc + 1 * c1pad + c, a1);
-                        atomicAdd(sacc + 2 * c1pad + c, a2);
-                        atomicAdd(sacc + 3 * c1pad + c, a3);
-                        atomicAdd(sacc + 4 * c1pad + c, a4);
-                        atomicAdd(sacc + 5 * c1pad + c, a5);
+                        tc::red_shared_f32(sacc + 0 * c1pad + c, a0);
+                        tc::red_shared_f32(sacc + 1 * c1pad + c, a1);
+                        tc::red_shared_f32(sacc + 2 * c1pad + c, a2);
+                        tc::red_shared_f32(sacc + 3 * c1pad + c, a3);
+                        tc::red_shared_f32(sacc + 4 * c1pad + c, a4);
+                        tc::red_shared_f32(sacc + 5 * c1pad + c, a5);
                     }
                 }
             }

@@ -225,24 +225,30 @@ tc_cm_gemm_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constan
                 tc::tmem_ld_wait();
                 float x[32];
 #pragma unroll
-                for (int j = 0; j < 32; ++j) x[j] = fmaf(ep_ss[cb + j], __uint_as_float(v[j]), ep_ss[256 + cb + j]);
+                for (int j = 0; j < 32; j += 4) {   // (explicit ld.shared: see tc_ptx.cuh)
+                    const float4 sc = tc::lds_f4_ro(ep_ss + cb + j), sh = tc::lds_f4_ro(ep_ss + 256 + cb + j);
+                    x[j] = fmaf(sc.x, __uint_as_float(v[j]), sh.x);
+                    x[j + 1] = fmaf(sc.y, __uint_as_float(v[j + 1]), sh.y);
+                    x[j + 2] = fmaf(sc.z, __uint_as_float(v[j + 2]), sh.z);
+                    x[j + 3] = fmaf(sc.w, __uint_as_float(v[j + 3]), sh.w);
+                }
                 if (p.stats != nullptr) {
                     // per-channel sum and sum of squares over this warp's 32 rows: 32x32 transpose through padded shared
                     // memory (conflict-free both ways), lane j then owns column cb + j
                     __syncwarp();
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) trw[lane * 33 + j] = valid ? x[j] : 0.f;
+                    for (int j = 0; j < 32; ++j) tc::sts_f(trw + lane * 33 + j, valid ? x[j] : 0.f);
                     __syncwarp();
                     float s1 = 0.f, s2 = 0.f;
 #pragma unroll
                     for (int r = 0; r < 32; ++r) {
-                        const float t = trw[r * 33 + lane];
+                        const float t = tc::lds_f(trw + r * 33 + lane);
                         s1 += t;
                         s2 = fmaf(t, t, s2);
                     }
                     if (cb + lane < Cout) {
-                        atomicAdd(&st_acc[cb + lane], (double)s1);
-                        atomicAdd(&st_acc[256 + cb + lane], (double)s2);
+                        tc::red_shared_f64(&st_acc[cb + lane], (double)s1);
+                        tc::red_shared_f64(&st_acc[256 + cb + lane], (double)s2);
                     }
                 }
                 if (EPI == CM_PMAX) {

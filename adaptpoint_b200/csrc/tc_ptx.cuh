@@ -178,16 +178,16 @@ __device__ __forceinline__ void st_shared_v4(uint32_t saddr, uint32_t a, uint32_
 }
 // Shared-memory loads with an explicit state space: pointers derived from the aligned dynamic-smem base through integer
 // casts lose it, and the compiler then emits generic LD.E (longer latency than LDS).
-// *_ro: data that is constant after the kernel's prologue (the compiler may move / merge these loads);
-// the others are ordered like volatile accesses (buffers rewritten between barriers).
+// *_ro: data that is constant after the kernel's prologue (volatile so that they stay behind the prologue's barrier, but
+// without a memory clobber); the others also order against surrounding memory accesses (buffers rewritten between barriers).
 __device__ __forceinline__ float4 lds_f4_ro(const float *p) {
     float4 r;
-    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(smem_u32(p)));
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(smem_u32(p)));
     return r;
 }
 __device__ __forceinline__ float lds_f_ro(const float *p) {
     float r;
-    asm("ld.shared.f32 %0, [%1];" : "=f"(r) : "r"(smem_u32(p)));
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(r) : "r"(smem_u32(p)));
     return r;
 }
 __device__ __forceinline__ float lds_f(const float *p) {
@@ -199,6 +199,18 @@ __device__ __forceinline__ int lds_i(const int *p) {
     int r;
     asm volatile("ld.shared.s32 %0, [%1];" : "=r"(r) : "r"(smem_u32(p)) : "memory");
     return r;
+}
+__device__ __forceinline__ void sts_f(float *p, float v) {
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(smem_u32(p)), "f"(v) : "memory");
+}
+__device__ __forceinline__ void sts_i(int *p, int v) {
+    asm volatile("st.shared.s32 [%0], %1;" ::"r"(smem_u32(p)), "r"(v) : "memory");
+}
+__device__ __forceinline__ void red_shared_f32(float *p, float v) {
+    asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(smem_u32(p)), "f"(v) : "memory");
+}
+__device__ __forceinline__ void red_shared_f64(double *p, double v) {
+    asm volatile("red.shared.add.f64 [%0], %1;" ::"r"(smem_u32(p)), "d"(v) : "memory");
 }
 __device__ __forceinline__ bool elect_one() {
     uint32_t pred;
