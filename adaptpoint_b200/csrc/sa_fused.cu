@@ -273,10 +273,10 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
                 }
             } else {
                 const int mb = (lt / NGROUPS) & 1;
-                g_meta_row[mb * BM + pt] = nx_urow;
-                g_meta_dp[(mb * 3 + 0) * BM + pt] = nx_dx;
-                g_meta_dp[(mb * 3 + 1) * BM + pt] = nx_dy;
-                g_meta_dp[(mb * 3 + 2) * BM + pt] = nx_dz;
+                tc::sts_i(g_meta_row + mb * BM + pt, nx_urow);
+                tc::sts_f(g_meta_dp + (mb * 3 + 0) * BM + pt, nx_dx);
+                tc::sts_f(g_meta_dp + (mb * 3 + 1) * BM + pt, nx_dy);
+                tc::sts_f(g_meta_dp + (mb * 3 + 2) * BM + pt, nx_dz);
                 named_bar_sync(1 + grp, 128);
                 fetch_meta(tile + (long long)NGROUPS * gridDim.x);  // next tile of this group, consumed next round
                 // 8 lanes per row, 8 channels (32 B of U) per lane; a warp covers 4 rows per step
@@ -292,7 +292,7 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
 #pragma unroll
                     for (int step = 0; step < 8; ++step) {
                         const int r = pw * 32 + step * 4 + lr;
-                        ur[step] = g_meta_row[mb * BM + r];
+                        ur[step] = tc::lds_i(g_meta_row + mb * BM + r);
                         const float4 *up = reinterpret_cast<const float4 *>(
                             p.U + (size_t)(ur[step] < 0 ? 0 : ur[step]) * p.C1 + (cvalid ? c0 : 0));
                         u0[step] = __ldg(up);
@@ -301,11 +301,11 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
                     float ps[8], pt1[8], wx[8], wy[8], wz[8];
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
-                        const float4 a = *reinterpret_cast<const float4 *>(prm + 0 * c1pad + c0 + 4 * h);
-                        const float4 bq = *reinterpret_cast<const float4 *>(prm + 1 * c1pad + c0 + 4 * h);
-                        const float4 cx = *reinterpret_cast<const float4 *>(prm + 2 * c1pad + c0 + 4 * h);
-                        const float4 cy = *reinterpret_cast<const float4 *>(prm + 3 * c1pad + c0 + 4 * h);
-                        const float4 cz = *reinterpret_cast<const float4 *>(prm + 4 * c1pad + c0 + 4 * h);
+                        const float4 a = tc::lds_f4_ro(prm + 0 * c1pad + c0 + 4 * h);
+                        const float4 bq = tc::lds_f4_ro(prm + 1 * c1pad + c0 + 4 * h);
+                        const float4 cx = tc::lds_f4_ro(prm + 2 * c1pad + c0 + 4 * h);
+                        const float4 cy = tc::lds_f4_ro(prm + 3 * c1pad + c0 + 4 * h);
+                        const float4 cz = tc::lds_f4_ro(prm + 4 * c1pad + c0 + 4 * h);
                         ps[4 * h + 0] = a.x; ps[4 * h + 1] = a.y; ps[4 * h + 2] = a.z; ps[4 * h + 3] = a.w;
                         pt1[4 * h + 0] = bq.x; pt1[4 * h + 1] = bq.y; pt1[4 * h + 2] = bq.z; pt1[4 * h + 3] = bq.w;
                         wx[4 * h + 0] = cx.x; wx[4 * h + 1] = cx.y; wx[4 * h + 2] = cx.z; wx[4 * h + 3] = cx.w;
@@ -317,9 +317,9 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
 #pragma unroll
                     for (int step = 0; step < 8; ++step) {
                         const int r = pw * 32 + step * 4 + lr;
-                        const float dx = g_meta_dp[(mb * 3 + 0) * BM + r];
-                        const float dy = g_meta_dp[(mb * 3 + 1) * BM + r];
-                        const float dz = g_meta_dp[(mb * 3 + 2) * BM + r];
+                        const float dx = tc::lds_f(g_meta_dp + (mb * 3 + 0) * BM + r);
+                        const float dy = tc::lds_f(g_meta_dp + (mb * 3 + 1) * BM + r);
+                        const float dz = tc::lds_f(g_meta_dp + (mb * 3 + 2) * BM + r);
                         float v[8] = {u0[step].x, u0[step].y, u0[step].z, u0[step].w,
                                       u1[step].x, u1[step].y, u1[step].z, u1[step].w};
                         const bool live = ur[step] >= 0 && cvalid;
@@ -366,7 +366,7 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
                     int mine = INT_MIN;
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
-                        const float x = fmaf(ep_ss[cb + j], __uint_as_float(v[j]), ep_ss[512 + cb + j]);
+                        const float x = fmaf(tc::lds_f_ro(ep_ss + cb + j), __uint_as_float(v[j]), tc::lds_f_ro(ep_ss + 512 + cb + j));
                         const int r = __reduce_max_sync(0xffffffffu, tc::float_to_ordered(x));
                         if (lane == j) mine = r;
                     }
@@ -388,7 +388,7 @@ tc_rows_gemm_kernel(const __grid_constant__ CUtensorMap wmap, const TcParams p) 
                     float x[32];
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
-                        const float t = fmaf(ep_ss[cb + j], __uint_as_float(v[j]), ep_ss[512 + cb + j]);
+                        const float t = fmaf(tc::lds_f_ro(ep_ss + cb + j), __uint_as_float(v[j]), tc::lds_f_ro(ep_ss + 512 + cb + j));
                         x[j] = p.relu ? fmaxf(t, 0.f) : t;
                     }
                     if (EPI == EPI_STORE_CM) {
